@@ -1,0 +1,195 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import mel_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4   # BASELINE.json north_star: max abs error on log-mel vs the reference's torchaudio path
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import xtts_b200._cabi as cabi
+    cabi.lib()          # fail loudly if the extension is missing
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def v1(dev):
+    from xtts_b200 import TorchMelSpectrogram
+    m = TorchMelSpectrogram(mel_norm_file=None)
+    m.mel_norms = torch.from_numpy(orc.default_mel_norms(80))
+    return m
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def test_c1_golden(dev, v1, golden_dir):
+    g = np.load(f"{golden_dir}/v1_c1_uniform_10s.npz")
+    x = orc.synth("uniform", 1, 220500, 1234)
+    y = v1(torch.from_numpy(x).to(dev))
+    assert tuple(y.shape) == g["mel"].shape == (1, 80, 862)
+    assert y.stride() == (862 * 80, 1, 80)          # the reference's transposed view
+    assert np.abs(_np(y) - g["mel"]).max() <= TOL
+    v1.mel_norms = None
+    y0 = v1(torch.from_numpy(x).to(dev))
+    assert np.abs(_np(y0) - g["mel_nonorm"]).max() <= TOL
+    v1.mel_norms = torch.from_numpy(orc.default_mel_norms(80))
+
+
+def test_edge_lengths_golden(dev, v1, golden_dir):
+    g = np.load(f"{golden_dir}/v1_edge_lengths.npz")
+    for L in (513, 600, 767, 768, 769, 1023, 1024, 1025, 1279, 1280, 1281, 2047, 2048, 4099):
+        y = v1(torch.from_numpy(g[f"x_{L}"]).to(dev))
+        ref = g[f"y_{L}"]
+        assert tuple(y.shape) == ref.shape, L        # bit-exact frame counts
+        assert np.abs(_np(y) - ref).max() <= TOL, L
+
+
+def test_signal_classes_golden(dev, v1, golden_dir):
+    g = np.load(f"{golden_dir}/v1_signals.npz")
+    y = v1(torch.from_numpy(g["x_gauss"]).to(dev))
+    assert np.abs(_np(y) - g["y_gauss"]).max() <= TOL
+    y = v1(torch.from_numpy(g["x_b1l"]).to(dev))      # [B,1,L] form
+    assert np.abs(_np(y) - g["y_b1l"]).max() <= TOL
+    # digital silence -> exactly log(1e-5)/norm everywhere
+    y = v1(torch.from_numpy(g["x_silence"]).to(dev))
+    assert np.array_equal(_np(y), g["y_silence"])
+    # tonal input: dual-oracle rule (SURVEY 8c ii)
+    x = g["x_tone"]
+    y = _np(v1(torch.from_numpy(x).to(dev))).astype(np.float64)
+    truth = orc.restated_logmel(x, orc.V1, g["norms"])
+    bound = np.maximum(TOL, 1.5 * np.abs(g["y_tone"].astype(np.float64) - truth))
+    assert (np.abs(y - truth) <= bound).all()
+
+
+def test_dvae_twin_golden(dev, golden_dir):
+    from xtts_b200 import dvae_wav_to_mel
+    g = np.load(f"{golden_dir}/v1_dvae_wav_to_mel.npz")
+    y = dvae_wav_to_mel(torch.from_numpy(g["x"]), mel_norms=torch.from_numpy(g["norms"]), device=dev)
+    assert np.abs(_np(y) - g["y"]).max() <= TOL
+
+
+def test_v2_features_golden(dev, golden_dir):
+    from xtts_b200 import MelSpectrogramFeatures
+    g = np.load(f"{golden_dir}/v2_features.npz")
+    mc, ms = MelSpectrogramFeatures(), MelSpectrogramFeatures(padding="same")
+    for L in (24000, 5000, 1024, 777):
+        x = torch.from_numpy(g[f"x_{L}"]).to(dev)
+        yc, ys = mc(x), ms(x)
+        assert tuple(yc.shape) == g[f"center_{L}"].shape and tuple(ys.shape) == g[f"same_{L}"].shape
+        assert np.abs(_np(yc) - g[f"center_{L}"]).max() <= TOL, L
+        assert np.abs(_np(ys) - g[f"same_{L}"]).max() <= TOL, L
+
+
+@pytest.mark.parametrize("kind", ["uniform", "gauss"])
+def test_dense_batch_vs_oracle(dev, v1, kind):
+    x = orc.synth(kind, 6, 33000, 42)
+    y = v1(torch.from_numpy(x).to(dev))
+    ref = orc.callsite_logmel(x, orc.V1, orc.default_mel_norms(80)).numpy()
+    assert tuple(y.shape) == ref.shape
+    assert np.abs(_np(y) - ref).max() <= TOL
+
+
+def test_ragged_batch_masks_and_values(dev, v1):
+    rng = np.random.default_rng(3)
+    lens = [513, 514, 767, 768, 1024, 20000, 9999, 12800, 12799, 12801, 2560, 700]
+    x = orc.synth("uniform", len(lens), max(lens), 8)
+    for b, L in enumerate(lens):
+        x[b, L:] = rng.random(max(lens) - L, dtype=np.float32)       # garbage beyond the clip must not matter
+    y, nf, mask = v1(torch.from_numpy(x).to(dev), lengths=torch.tensor(lens))
+    ry, rn, rmask = orc.callsite_logmel_ragged(x, lens, orc.V1, orc.default_mel_norms(80))
+    assert nf.dtype == torch.int64 and nf.cpu().tolist() == rn.tolist()       # bit-exact frame counts
+    assert mask.dtype == torch.bool and np.array_equal(_np(mask), rmask)      # bit-exact padding masks
+    assert tuple(y.shape) == tuple(ry.shape)
+    assert np.abs(_np(y) - ry.numpy()).max() <= TOL
+    assert (_np(y)[rmask[:, None, :].repeat(80, 1)] == 0.0).all()             # padded frames are 0.0
+
+
+def test_dft_stage_vs_fp64(dev):
+    from xtts_b200 import MelPlan
+    plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0,
+                   f_max=8000, power=2.0, norm="slaney", device=dev)
+    x = orc.synth("uniform", 2, 9000, 17)
+    out, nf, _, reim = plan.forward(torch.from_numpy(x).to(dev), debug_reim=True)
+    plan.status()
+    T = int(nf[0])
+    k0, live, nbt = plan.first_bin, plan.live_bins, plan.num_bins
+    assert (k0, live) == (1, 371)
+    for b in range(2):
+        st = orc.restated_stages(x[b], orc.V1)
+        re = _np(reim[b * T:(b + 1) * T, :live])
+        im = _np(reim[b * T:(b + 1) * T, nbt:nbt + live])
+        scale = np.abs(st.re).max()
+        assert np.abs(re - st.re[:, k0:k0 + live]).max() <= 2e-6 * scale
+        assert np.abs(im + st.im[:, k0:k0 + live]).max() <= 2e-6 * scale
+
+
+def test_simt_crosscheck_full_size(dev, v1):
+    """Config 2 (64 x 10 s): the tcgen05 kernel against the independent CUDA-core kernel."""
+    plan = v1._plan_for(dev)
+    g = torch.Generator(device=dev).manual_seed(1234)
+    x = torch.rand(64, 220500, device=dev, generator=g) * 2 - 1
+    a, nfa, _ = plan.forward(x, impl="tcgen05")
+    b, nfb, _ = plan.forward(x, impl="simt")
+    plan.status()
+    assert a.shape == (64, 862, 80) and torch.equal(nfa, nfb)
+    assert float((a - b).abs().max()) <= TOL
+    # 16-clip sample against the oracle itself
+    idx = list(range(0, 64, 4))
+    ref = orc.callsite_logmel(x[idx].cpu().numpy(), orc.V1, orc.default_mel_norms(80)).numpy()
+    assert np.abs(_np(a[idx].transpose(1, 2)) - ref).max() <= TOL
+
+
+def test_long_form_linearity_and_shift(dev):
+    """Config 5 shape (120 s clips): size-independent properties instead of a CPU oracle run."""
+    from xtts_b200 import TorchMelSpectrogram
+    m = TorchMelSpectrogram(mel_norm_file=None)
+    g = torch.Generator(device=dev).manual_seed(7)
+    x = torch.rand(4, 2646000, device=dev, generator=g) * 2 - 1
+    y = m(x)
+    assert tuple(y.shape) == (4, 80, 10336)
+    # power spectrum scales with the square of the gain: log-mel shifts by 2*log(g)
+    y2 = m(x * 0.5)
+    assert float((y2 - (y + 2 * np.log(0.5))).abs().max()) <= 2e-5
+    # a shift by exactly one hop moves interior frames by one
+    y3 = m(x[:, 256:])
+    assert float((y3[:, :, 2:1000] - y[:, :, 3:1001]).abs().max()) <= 2e-5
+    # spot-check one clip prefix against the oracle (frames away from the right edge are identical)
+    ref = orc.callsite_logmel(x[:1, :220500].cpu().numpy(), orc.V1, None).numpy()
+    assert np.abs(_np(y[:1, :, :850]) - ref[:, :, :850]).max() <= TOL
+
+
+def test_error_behaviour(dev, v1):
+    with pytest.raises(AssertionError):
+        v1(torch.zeros(2, 2, 2, 2000, device=dev))
+    with pytest.raises(RuntimeError):
+        v1(torch.zeros(1, 512, device=dev))             # reflect pad needs L > 512
+    with pytest.raises(RuntimeError):
+        v1(torch.zeros(1, 4000))                        # CPU tensor: no fallback
+    with pytest.raises(RuntimeError):
+        v1(torch.zeros(1, 4000, device=dev, dtype=torch.float64))
+    y = v1(torch.zeros(1, 4000, device=dev, dtype=torch.float16))
+    assert y.dtype == torch.float32
+
+
+def test_mel_stats(dev):
+    from xtts_b200 import MelPlan
+    plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0,
+                   f_max=8000, power=2.0, norm="slaney", device=dev)
+    lens = [22050, 8000, 15000, 513]
+    x = orc.synth("uniform", 4, 22050, 77)
+    out, nf, _ = plan.forward(torch.from_numpy(x).to(dev), torch.tensor(lens), t_max=plan.frames(22050))
+    acc = torch.zeros(161, dtype=torch.float64, device=dev)
+    plan.stats_accumulate(out, nf, acc)
+    plan.stats_accumulate(out, nf, acc)          # accumulates (not zeroed by the call)
+    ref = orc.mel_stats(_np(out).transpose(0, 2, 1), _np(nf))
+    got = acc.cpu().numpy() / 2
+    assert got[160] == ref[160] == sum(orc.frame_count(L) for L in lens)
+    assert np.allclose(got[:160], ref[:160], rtol=1e-12, atol=1e-9)

@@ -1,0 +1,74 @@
+"""ctypes binding of the C ABI in ``include/ttts_mel.h`` (``libttts_mel.so``, built in-tree).
+
+There is no CPU implementation behind this module: if the shared library is missing or a call
+fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import (POINTER, Structure, c_char_p, c_double, c_float, c_int32, c_int64, c_size_t,
+                    c_uint8, c_void_p)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libttts_mel.so")
+
+OK, EINVAL, ECUDA, ENOMEM, EDEVICE = 0, -1, -2, -3, -4
+
+
+class MelConfig(Structure):
+    _fields_ = [("n_fft", c_int32), ("hop", c_int32), ("n_mels", c_int32), ("pad", c_int32),
+                ("power", c_float), ("clamp", c_float), ("spec_scale", c_float)]
+
+
+class MelError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"ttts_mel error {code}: {msg}")
+        self.code = code
+
+
+_FWD_ARGS = [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int64, c_int32, c_void_p, c_void_p,
+             c_void_p, c_void_p, c_size_t, c_void_p]
+
+SYMBOLS = {
+    "ttts_mel_plan_create": (ctypes.c_int, [POINTER(MelConfig), c_void_p, c_void_p, POINTER(c_void_p)]),
+    "ttts_mel_plan_set_norms": (ctypes.c_int, [c_void_p, c_void_p]),
+    "ttts_mel_plan_destroy": (None, [c_void_p]),
+    "ttts_mel_frames": (c_int64, [c_void_p, c_int64]),
+    "ttts_mel_workspace_bytes": (c_size_t, [c_void_p, c_int32, c_int64]),
+    "ttts_mel_forward": (ctypes.c_int, _FWD_ARGS),
+    "ttts_mel_forward_simt": (ctypes.c_int, _FWD_ARGS),
+    "ttts_mel_forward_debug": (ctypes.c_int, _FWD_ARGS + [c_void_p]),
+    "ttts_mel_first_bin": (c_int32, [c_void_p]),
+    "ttts_mel_num_bins": (c_int32, [c_void_p]),
+    "ttts_mel_live_bins": (c_int32, [c_void_p]),
+    "ttts_mel_status": (ctypes.c_int, [c_void_p, c_void_p]),
+    "ttts_mel_stats_accumulate": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p]),
+    "ttts_mel_last_launch_count": (c_int32, []),
+    "ttts_mel_last_error": (c_char_p, []),
+    "ttts_mel_version": (c_char_p, []),
+}
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """Load the library once; raise loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a).  There is no CPU fallback for this path.")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(handle, name)      # AttributeError if the header and the library disagree
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != OK:
+        raise MelError(int(rc), lib().ttts_mel_last_error().decode("utf-8", "replace"))

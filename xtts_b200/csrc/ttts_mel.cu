@@ -1,0 +1,1018 @@
+// ttts_mel.cu -- B200 (sm_100a) batched log-mel front-end behind the C ABI of include/ttts_mel.h.
+//
+// Replaces, for the path TorchMelSpectrogram.forward (ttts/utils/utils.py:509-522) takes through
+// torchaudio/torch.stft/matmul, the whole chain reflect-pad -> frame -> Hann -> rDFT -> |.|^p ->
+// mel filterbank -> log(clamp) -> / mel_norms with five kernels:
+//
+//   k_prep    lengths -> n_frames (torch.stft frame count) + exclusive prefix (frame -> clip map)
+//   k_pad     per-clip reflect padding into a workspace signal (128-bit coalesced loads/stores)
+//   k_logmel  the fused hot kernel (persistent, warp-specialised, one CTA per SM):
+//               loader warp     cp.async 16 B gathers of the overlapping hop windows -> smem ring
+//               converter warps even/odd fold  E[n]=f[n]+f[N-n], O[n]=f[n]-f[N-n]  (halves K),
+//                               TF32 hi/lo split, tcgen05.st into TMEM (A operand never in smem)
+//               TMA warp        cp.async.bulk of pre-tiled windowed cos/sin basis stages -> smem ring
+//               MMA thread      tcgen05.mma kind::tf32, A from TMEM, B from smem, fp32 accumulators in
+//                               TMEM; 3-term error-compensated product hi*hi + lo*hi + hi*lo
+//               epilogue warps  tcgen05.ld -> re^2+im^2 -> sparse mel contraction -> log(clamp) -> /norm
+//             spectrum magnitudes never leave the SM.
+//   k_simt    the same maths on CUDA cores in plain fp32 (independent cross-check, not a fallback)
+//   k_stats   per-channel sum / sum-of-squares / count of log-mel for mel_norms
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include "ttts_mel.h"
+
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+// ------------------------------------------------------------------------------------------
+// constants of the tiling
+// ------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kNfft = 1024;            // the only transform size built this round
+constexpr int kHop = 256;
+constexpr int kKfold = kNfft / 2;      // folded contraction length (kappa = n-1, n = 1..512)
+constexpr int kTileM = 128;            // frames per tile == TMEM lanes
+constexpr int kKC = 16;                // kappa per A (TMEM) stage and per raw-audio stage
+constexpr int kKStep = 8;              // K of one tcgen05.mma kind::tf32
+constexpr int kChunks = kKfold / kKC;  // 32 chunks per pass
+constexpr int kKSteps = kKfold / kKStep;  // 64 basis stages per pass
+constexpr int kNBMax = 192;            // bins per pass (accumulator columns: re | im)
+constexpr int kBStages = 5;            // basis ring depth (one k-step each)
+constexpr int kRawStages = 4;          // raw-audio ring depth (one chunk each)
+constexpr int kRawPitch = 20;          // floats per staged row (80 B: conflict-free row-per-thread LDS.128)
+constexpr int kRawStageBytes = 2 * kTileM * kRawPitch * 4;   // forward window + mirrored window
+constexpr int kTmemCols = 512;
+constexpr int kColIm = kNBMax;         // accumulator columns: re [0,NB), im [192,192+NB)
+constexpr int kColA = 2 * kNBMax;      // A ring: 2 stages x 64 columns (E_hi,E_lo,O_hi,O_lo x 16)
+constexpr int kThreads = 512;
+constexpr int kMaxMels = 128;
+constexpr long long kTimeoutCycles = 4000000000LL;
+
+// warp roles of k_logmel
+constexpr int kWarpTma = 0, kWarpMma = 1, kWarpTmem = 2, kWarpLoad = 3;
+constexpr int kWarpConv0 = 4;          // 8 converter warps: 4..11   (warp % 4 == TMEM lane quarter)
+constexpr int kWarpEpi0 = 12;          // 4 epilogue warps: 12..15
+
+thread_local char g_err[512] = "";
+thread_local int g_launches = 0;
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t e_ = (expr);                                                                    \
+    if (e_ != cudaSuccess) return fail(TTTS_MEL_ECUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+struct ttts_mel_plan {
+  ttts_mel_config cfg;
+  int device = 0;
+  int num_sms = 0;
+  int kmin = 0;        // first live bin
+  int n_live = 0;      // live bins (kmin .. kmin+n_live-1)
+  int passes = 0;      // accumulator passes over the bin axis
+  int nb = 0;          // bins per pass (multiple of 16, <= 192)
+  int nbt = 0;         // passes * nb
+  float* d_basis = nullptr;    // [passes][64 k-steps][4 arrays][2 k-halves][nb][4] fp32 (TF32-exact values)
+  float4* d_meltab = nullptr;  // [nbt] {w_lo, w_hi, bits(filter_lo), 0}
+  float* d_norms = nullptr;    // [n_mels] or nullptr
+  float* d_cosf = nullptr;     // [512][nbt] plain fp32 folded basis for k_simt
+  float* d_sinf = nullptr;
+  float* d_fb = nullptr;       // [nbt][n_mels] dense filterbank rows of the live bins for k_simt
+};
+
+// ------------------------------------------------------------------------------------------
+// host: plan construction
+// ------------------------------------------------------------------------------------------
+namespace {
+
+// round-to-nearest to TF32 (10 explicit mantissa bits); result is exactly representable in TF32
+float tf32_rn(double v) {
+  float f = (float)v;
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  u = (u + 0x1000u) & 0xFFFFE000u;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+}  // namespace
+
+extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb, const float* window,
+                                    ttts_mel_plan** out) {
+  if (!cfg || !fb || !window || !out) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (cfg->n_fft != kNfft || cfg->hop != kHop)
+    return fail(TTTS_MEL_EINVAL, "unsupported n_fft/hop %d/%d (built: %d/%d)", cfg->n_fft, cfg->hop, kNfft, kHop);
+  if (cfg->n_mels < 1 || cfg->n_mels > kMaxMels) return fail(TTTS_MEL_EINVAL, "n_mels %d not in [1,%d]", cfg->n_mels, kMaxMels);
+  if (cfg->pad < 0 || cfg->pad > kNfft / 2 || cfg->pad % 4 != 0)
+    return fail(TTTS_MEL_EINVAL, "pad %d must be a multiple of 4 in [0,%d]", cfg->pad, kNfft / 2);
+  if (!(cfg->power == 1.0f || cfg->power == 2.0f)) return fail(TTTS_MEL_EINVAL, "power must be 1 or 2");
+  if (!(cfg->clamp > 0.f)) return fail(TTTS_MEL_EINVAL, "clamp must be > 0");
+  const int N = kNfft, nfreq = N / 2 + 1, nm = cfg->n_mels;
+
+  // The even/odd fold needs w[n] == w[N-n] and contributes nothing at n = 0 only if w[0] == 0.
+  double wmax = 0;
+  for (int n = 0; n < N; ++n) wmax = fmax(wmax, fabs((double)window[n]));
+  if (fabs((double)window[0]) > 1e-7 * wmax) return fail(TTTS_MEL_EINVAL, "window[0] must be 0 (periodic window)");
+  for (int n = 1; n < N; ++n)
+    if (fabs((double)window[n] - (double)window[N - n]) > 1e-6 * wmax)
+      return fail(TTTS_MEL_EINVAL, "window must satisfy w[n] == w[n_fft-n] (tap %d)", n);
+
+  // live bin range = rows of fb with any non-zero weight
+  int kmin = nfreq, kmax = -1;
+  for (int k = 0; k < nfreq; ++k)
+    for (int m = 0; m < nm; ++m)
+      if (fb[(size_t)k * nm + m] != 0.f) { kmin = k < kmin ? k : kmin; kmax = k; break; }
+  if (kmax < 0) return fail(TTTS_MEL_EINVAL, "filterbank is all zero");
+
+  ttts_mel_plan* p = new ttts_mel_plan();
+  p->cfg = *cfg;
+  p->kmin = kmin;
+  p->n_live = kmax - kmin + 1;
+  p->passes = (p->n_live + kNBMax - 1) / kNBMax;
+  p->nb = (int)align_up((size_t)((p->n_live + p->passes - 1) / p->passes), 16);
+  p->nbt = p->passes * p->nb;
+  const int nb = p->nb, nbt = p->nbt;
+
+  // sparse mel table: every bin feeds at most two ADJACENT filters (triangular filterbanks)
+  std::vector<float4> tab(nbt);
+  std::vector<float> fbl((size_t)nbt * nm, 0.f);
+  int cur = 0;
+  for (int i = 0; i < nbt; ++i) {
+    float wlo = 0.f, whi = 0.f;
+    if (i < p->n_live) {
+      const float* row = fb + (size_t)(kmin + i) * nm;
+      int first = -1, last = -1;
+      for (int m = 0; m < nm; ++m) {
+        fbl[(size_t)i * nm + m] = row[m];
+        if (row[m] != 0.f) { if (first < 0) first = m; last = m; }
+      }
+      if (first >= 0) {
+        if (last - first > 1 || first < cur) {
+          delete p;
+          return fail(TTTS_MEL_EINVAL, "filterbank row %d is not two adjacent, non-decreasing filters", kmin + i);
+        }
+        cur = first;
+        wlo = row[first];
+        whi = (last > first) ? row[last] : 0.f;
+      }
+    }
+    float4 t;
+    t.x = wlo; t.y = whi; t.z = 0.f; t.w = 0.f;
+    memcpy(&t.z, &cur, 4);
+    tab[i] = t;
+  }
+
+  // folded, windowed basis.  kappa = n-1 for n = 1..512;  the n = 512 tap appears once, so it
+  // carries the factor 1/2 (E[512] = 2 f[512]).  Trig argument reduced as an integer first.
+  std::vector<double> cb((size_t)kKfold * nbt, 0.0), sb((size_t)kKfold * nbt, 0.0);
+  const double scale = (double)cfg->spec_scale;
+  for (int kap = 0; kap < kKfold; ++kap) {
+    const int n = kap + 1;
+    const double w = 0.5 * ((double)window[n] + (double)window[N - n]) * (n == N / 2 ? 0.5 : 1.0) * scale;
+    for (int i = 0; i < p->n_live; ++i) {
+      const int k = kmin + i;
+      const int r = (int)(((long long)k * n) % N);
+      const double ang = 2.0 * M_PI * (double)r / (double)N;
+      cb[(size_t)kap * nbt + i] = w * cos(ang);
+      sb[(size_t)kap * nbt + i] = w * sin(ang);
+    }
+  }
+  std::vector<float> cosf((size_t)kKfold * nbt), sinf_((size_t)kKfold * nbt);
+  for (size_t j = 0; j < cosf.size(); ++j) { cosf[j] = (float)cb[j]; sinf_[j] = (float)sb[j]; }
+
+  // tiled stage images: [pass][kstep][array: C_hi, C_lo, S_hi, S_lo][k-half j][row][4 floats]
+  // = the UMMA K-major SWIZZLE_NONE canonical layout (8 rows x 16 B core matrices, LBO = nb*16 B
+  // between the two k-halves, SBO = 128 B between 8-row groups), so one bulk copy lands a stage.
+  const size_t stage_floats = (size_t)4 * 2 * nb * 4;
+  std::vector<float> img((size_t)p->passes * kKSteps * stage_floats);
+  for (int ps = 0; ps < p->passes; ++ps)
+    for (int ks = 0; ks < kKSteps; ++ks) {
+      float* st = img.data() + ((size_t)ps * kKSteps + ks) * stage_floats;
+      for (int arr = 0; arr < 4; ++arr)
+        for (int j = 0; j < 2; ++j)
+          for (int r = 0; r < nb; ++r)
+            for (int e = 0; e < 4; ++e) {
+              const int kap = ks * kKStep + j * 4 + e;
+              const double v = (arr < 2 ? cb : sb)[(size_t)kap * nbt + ps * nb + r];
+              const float hi = tf32_rn(v);
+              const float val = (arr & 1) ? tf32_rn(v - (double)hi) : hi;
+              st[(((size_t)arr * 2 + j) * nb + r) * 4 + e] = val;
+            }
+    }
+
+  cudaError_t e;
+  int dev = 0;
+  e = cudaGetDevice(&dev);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&p->num_sms, cudaDevAttrMultiProcessorCount, dev);
+  p->device = dev;
+  auto up = [&](void** dptr, const void* src, size_t bytes) {
+    if (e != cudaSuccess) return;
+    e = cudaMalloc(dptr, bytes);
+    if (e == cudaSuccess) e = cudaMemcpy(*dptr, src, bytes, cudaMemcpyHostToDevice);
+  };
+  up((void**)&p->d_basis, img.data(), img.size() * 4);
+  up((void**)&p->d_meltab, tab.data(), tab.size() * sizeof(float4));
+  up((void**)&p->d_cosf, cosf.data(), cosf.size() * 4);
+  up((void**)&p->d_sinf, sinf_.data(), sinf_.size() * 4);
+  up((void**)&p->d_fb, fbl.data(), fbl.size() * 4);
+  if (e != cudaSuccess) {
+    int rc = fail(TTTS_MEL_ECUDA, "plan upload: %s", cudaGetErrorString(e));
+    ttts_mel_plan_destroy(p);
+    return rc;
+  }
+  *out = p;
+  return TTTS_MEL_OK;
+}
+
+extern "C" int ttts_mel_plan_set_norms(ttts_mel_plan* p, const float* norms) {
+  if (!p) return fail(TTTS_MEL_EINVAL, "null plan");
+  if (!norms) {
+    if (p->d_norms) cudaFree(p->d_norms);
+    p->d_norms = nullptr;
+    return TTTS_MEL_OK;
+  }
+  if (!p->d_norms) CUDA_TRY(cudaMalloc((void**)&p->d_norms, p->cfg.n_mels * sizeof(float)));
+  CUDA_TRY(cudaMemcpy(p->d_norms, norms, p->cfg.n_mels * sizeof(float), cudaMemcpyHostToDevice));
+  return TTTS_MEL_OK;
+}
+
+extern "C" void ttts_mel_plan_destroy(ttts_mel_plan* p) {
+  if (!p) return;
+  cudaFree(p->d_basis); cudaFree(p->d_meltab); cudaFree(p->d_norms);
+  cudaFree(p->d_cosf); cudaFree(p->d_sinf); cudaFree(p->d_fb);
+  delete p;
+}
+
+extern "C" int64_t ttts_mel_frames(const ttts_mel_plan* p, int64_t length) {
+  if (!p) return fail(TTTS_MEL_EINVAL, "null plan");
+  if (length <= p->cfg.pad || length + 2 * p->cfg.pad < kNfft)
+    return fail(TTTS_MEL_EINVAL, "length %lld too short for reflect pad %d / n_fft %d", (long long)length, p->cfg.pad, kNfft);
+  return 1 + (length + 2 * p->cfg.pad - kNfft) / kHop;
+}
+
+extern "C" int32_t ttts_mel_first_bin(const ttts_mel_plan* p) { return p ? p->kmin : -1; }
+extern "C" int32_t ttts_mel_num_bins(const ttts_mel_plan* p) { return p ? p->nbt : -1; }
+extern "C" int32_t ttts_mel_live_bins(const ttts_mel_plan* p) { return p ? p->n_live : -1; }
+extern "C" const char* ttts_mel_last_error(void) { return g_err; }
+extern "C" const char* ttts_mel_version(void) { return "ttts_mel 0.1 (sm_100a, tcgen05 tf32x3)"; }
+extern "C" int32_t ttts_mel_last_launch_count(void) { return g_launches; }
+
+// ------------------------------------------------------------------------------------------
+// workspace
+// ------------------------------------------------------------------------------------------
+namespace {
+
+struct Workspace {
+  int32_t* status;      // [64] word 0 = device error code
+  int64_t* frame_off;   // [B+1]
+  int32_t* n_frames;    // [B]
+  float* xp;            // [B][Lp]
+  int64_t Lp;
+  size_t bytes;
+};
+
+Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
+  Workspace w{};
+  const int64_t T = 1 + (Lmax + 2 * p->cfg.pad - kNfft) / kHop;
+  w.Lp = (int64_t)align_up((size_t)(kHop * (T > 0 ? T - 1 : 0) + kNfft + 64), 64);
+  size_t off = 0;
+  char* b = (char*)base;
+  w.status = (int32_t*)(b + off); off += 256;
+  w.frame_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
+  w.n_frames = (int32_t*)(b + off); off += align_up((size_t)B * 4, 256);
+  w.xp = (float*)(b + off); off += align_up((size_t)B * (size_t)w.Lp * 4, 256);
+  w.bytes = off;
+  return w;
+}
+
+}  // namespace
+
+extern "C" size_t ttts_mel_workspace_bytes(const ttts_mel_plan* p, int32_t B, int64_t Lmax) {
+  if (!p || B <= 0 || Lmax <= 0) return 0;
+  return carve(p, nullptr, B, Lmax).bytes;
+}
+
+// ------------------------------------------------------------------------------------------
+// device helpers (PTX)
+// ------------------------------------------------------------------------------------------
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok;
+}
+// Bounded wait: a pipeline bug must surface as an error code, never as a hung GPU.
+__device__ __noinline__ void mbar_timeout(int32_t* status, int code) {
+  atomicExch(status, code);
+  __threadfence_system();
+  __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int32_t* status, int code) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
+  }
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T, kind::tf32, M = 128, K = 8
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d, uint32_t a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d), "r"(a), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+        "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// K-major, SWIZZLE_NONE shared-memory matrix descriptor (sm_100 format, version 1)
+__device__ __forceinline__ uint64_t make_bdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;   // descriptor version
+  return d;                 // base_offset 0, lbo_mode 0, layout_type 0 (no swizzle)
+}
+
+// round-to-nearest TF32 of an fp32 bit pattern
+__device__ __forceinline__ uint32_t tf32_bits(uint32_t u) { return (u + 0x1000u) & 0xFFFFE000u; }
+
+// frame index g (clips concatenated) -> clip b; frame_off is the exclusive prefix of n_frames
+__device__ __forceinline__ int find_clip(const int64_t* __restrict__ frame_off, int B, int64_t g) {
+  int lo = 0, hi = B - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (frame_off[mid] <= g) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// k_prep: lengths -> n_frames, frame_off (exclusive prefix), status
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_prep(const int64_t* __restrict__ lengths, int B, int64_t Lmax, int pad,
+                                               int Tmax, int32_t* __restrict__ n_frames,
+                                               int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
+                                               int32_t* __restrict__ status) {
+  __shared__ long long part[1024];
+  const int tid = threadIdx.x;
+  const int per = (B + 1023) / 1024;
+  const int b0 = tid * per, b1 = min(B, b0 + per);
+  long long sum = 0;
+  for (int b = b0; b < b1; ++b) {
+    const long long L = lengths ? lengths[b] : Lmax;
+    long long T = 0;
+    if (L > pad && L <= Lmax && L + 2 * pad >= kNfft) T = 1 + (L + 2 * pad - kNfft) / kHop;
+    else atomicExch(status, 1);                 // bad length
+    if (T > Tmax) { T = Tmax; atomicExch(status, 2); }
+    n_frames[b] = (int32_t)T;
+    if (n_frames_user) n_frames_user[b] = (int32_t)T;
+    sum += T;
+  }
+  part[tid] = sum;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const long long v = tid >= d ? part[tid - d] : 0;
+    __syncthreads();
+    part[tid] += v;
+    __syncthreads();
+  }
+  long long run = part[tid] - sum;
+  for (int b = b0; b < b1; ++b) { frame_off[b] = run; run += n_frames[b]; }
+  if (tid == 1023) frame_off[B] = part[1023];
+}
+
+// ------------------------------------------------------------------------------------------
+// k_pad: xp[b][i] = reflect-padded clip b (pad on each side at the clip's OWN length), 0 beyond
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_pad(const float* __restrict__ wav, int64_t row_stride,
+                                             const int64_t* __restrict__ lengths, int64_t Lmax, int pad,
+                                             float* __restrict__ xp, int64_t Lp, int vec_ok) {
+  const int b = blockIdx.y;
+  const int64_t L = lengths ? lengths[b] : Lmax;
+  const float* __restrict__ src = wav + (int64_t)b * row_stride;
+  float* __restrict__ dst = xp + (int64_t)b * Lp;
+  const bool okL = (L > pad) && (L <= Lmax);
+  for (int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i4 < Lp;
+       i4 += (int64_t)gridDim.x * blockDim.x * 4) {
+    float4 v;
+    const int64_t s0 = i4 - pad;
+    if (okL && vec_ok && s0 >= 0 && s0 + 3 < L) {
+      v = __ldg(reinterpret_cast<const float4*>(src + s0));
+    } else {
+      float t[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        int64_t s = s0 + e;
+        float val = 0.f;
+        if (okL && s >= -(int64_t)pad && s < L + pad) {
+          if (s < 0) s = -s;
+          if (s >= L) s = 2 * (L - 1) - s;
+          val = __ldg(src + s);
+        }
+        t[e] = val;
+      }
+      v = make_float4(t[0], t[1], t[2], t[3]);
+    }
+    *reinterpret_cast<float4*>(dst + i4) = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_mask: make_pad_mask (ttts/utils/utils.py:77-103): mask[b][t] = t >= n_frames[b]
+// ------------------------------------------------------------------------------------------
+__global__ void k_mask(const int32_t* __restrict__ n_frames, int B, int Tmax, uint8_t* __restrict__ mask) {
+  const int64_t total = (int64_t)B * Tmax;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / Tmax), t = (int)(i % Tmax);
+    mask[i] = t >= n_frames[b] ? 1 : 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_logmel: the fused tcgen05 kernel
+// ------------------------------------------------------------------------------------------
+struct LogmelParams {
+  const float* xp;            // [B][Lp] reflect-padded clips
+  int64_t Lp;
+  const int64_t* frame_off;   // [B+1]
+  const int32_t* n_frames;    // [B]
+  int B;
+  int Tmax;
+  float* out;                 // [B][Tmax][n_mels]
+  const float* basis;         // tiled stage images
+  const float4* meltab;       // [nbt]
+  const float* norms;         // [n_mels] or null
+  int passes, nb, nbt, n_mels;
+  float clamp;
+  int power_is_1;
+  int32_t* status;
+  float* dbg_reim;            // optional [total_frames][2*nbt]
+};
+
+struct __align__(8) LogmelBarriers {
+  uint64_t b_full[kBStages], b_empty[kBStages];
+  uint64_t raw_full[kRawStages], raw_empty[kRawStages];
+  uint64_t a_full[2], a_empty[2];
+  uint64_t acc_full, acc_empty;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  // ---- carve shared memory
+  const int nb = P.nb;
+  const uint32_t b_stage_bytes = (uint32_t)nb * 128u;       // 4 arrays x 2 k-halves x nb rows x 16 B
+  uint8_t* s_b = smem;                                       // basis ring
+  uint8_t* s_raw = s_b + (size_t)kBStages * b_stage_bytes;   // raw audio ring
+  float4* s_tab = reinterpret_cast<float4*>(s_raw + (size_t)kRawStages * kRawStageBytes);
+  float* s_norm = reinterpret_cast<float*>(s_tab + P.nbt);
+  int32_t* s_rowbase = reinterpret_cast<int32_t*>(s_norm + kMaxMels);
+  LogmelBarriers* bars = reinterpret_cast<LogmelBarriers*>(s_rowbase + kTileM);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t total_frames = P.frame_off[P.B];
+  const int num_tiles = (int)((total_frames + kTileM - 1) / kTileM);
+
+  // ---- one-time setup
+  for (int i = threadIdx.x; i < P.nbt; i += kThreads) s_tab[i] = P.meltab[i];
+  for (int i = threadIdx.x; i < P.n_mels; i += kThreads) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kBStages; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
+    for (int i = 0; i < kRawStages; ++i) { mbar_init(smem_u32(&bars->raw_full[i]), 32); mbar_init(smem_u32(&bars->raw_empty[i]), 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
+    mbar_init(smem_u32(&bars->acc_full), 1);
+    mbar_init(smem_u32(&bars->acc_empty), 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpTmem) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *s_tmem;
+
+  if (warp == kWarpTma) {
+    // ===== basis producer: one bulk copy per k-step stage =====
+    if (lane == 0) {
+      uint32_t seq = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+        for (int ps = 0; ps < P.passes; ++ps)
+          for (int ks = 0; ks < kKSteps; ++ks, ++seq) {
+            const uint32_t st = seq % kBStages, use = seq / kBStages;
+            mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
+            const uint32_t full = smem_u32(&bars->b_full[st]);
+            mbar_expect_tx(full, b_stage_bytes);
+            bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
+                     P.basis + ((size_t)ps * kKSteps + ks) * (b_stage_bytes / 4), b_stage_bytes, full);
+          }
+    }
+    __syncwarp();
+  } else if (warp == kWarpMma) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nb >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+      const uint32_t lbo = (uint32_t)nb * 16u, sbo = 128u, arr_bytes = (uint32_t)nb * 32u;
+      const uint32_t d_re = tmem, d_im = tmem + kColIm;
+      uint32_t bseq = 0, cseq = 0, pseq = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+        for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+          mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+          tc_fence_after();
+          for (int c = 0; c < kChunks; ++c, ++cseq) {
+            const uint32_t as = cseq & 1, ause = cseq >> 1;
+            mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+            tc_fence_after();
+            const uint32_t a_base = tmem + kColA + as * 64;
+#pragma unroll
+            for (int kk = 0; kk < kKC / kKStep; ++kk, ++bseq) {
+              const uint32_t st = bseq % kBStages, use = bseq / kBStages;
+              mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+              tc_fence_after();
+              const uint32_t sb_addr = smem_u32(s_b + (size_t)st * b_stage_bytes);
+              const uint64_t c_hi = make_bdesc(sb_addr, lbo, sbo);
+              const uint64_t c_lo = make_bdesc(sb_addr + arr_bytes, lbo, sbo);
+              const uint64_t s_hi = make_bdesc(sb_addr + 2 * arr_bytes, lbo, sbo);
+              const uint64_t s_lo = make_bdesc(sb_addr + 3 * arr_bytes, lbo, sbo);
+              const uint32_t e_hi = a_base + 0 + kk * kKStep, e_lo = a_base + 16 + kk * kKStep;
+              const uint32_t o_hi = a_base + 32 + kk * kKStep, o_lo = a_base + 48 + kk * kKStep;
+              const uint32_t first = (c == 0 && kk == 0) ? 0u : 1u;
+              mma_tf32_ts(d_re, e_lo, c_hi, idesc, first);   // small terms first
+              mma_tf32_ts(d_re, e_hi, c_lo, idesc, 1u);
+              mma_tf32_ts(d_re, e_hi, c_hi, idesc, 1u);
+              mma_tf32_ts(d_im, o_lo, s_hi, idesc, first);
+              mma_tf32_ts(d_im, o_hi, s_lo, idesc, 1u);
+              mma_tf32_ts(d_im, o_hi, s_hi, idesc, 1u);
+              tc_commit(smem_u32(&bars->b_empty[st]));       // basis stage free once these MMAs retire
+            }
+            tc_commit(smem_u32(&bars->a_empty[as]));         // A stage free
+          }
+          tc_commit(smem_u32(&bars->acc_full));              // accumulators of this pass complete
+        }
+    }
+    __syncwarp();
+  } else if (warp == kWarpLoad) {
+    // ===== raw-audio loader: cp.async gathers of the hop windows of 128 frames =====
+    uint32_t cseq = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < kTileM / 32; ++i) {
+        const int r = lane + 32 * i;
+        const int64_t g = (int64_t)tile * kTileM + r;
+        int32_t base = -1;
+        if (g < total_frames) {
+          const int b = find_clip(P.frame_off, P.B, g);
+          base = (int32_t)((int64_t)b * P.Lp + (g - P.frame_off[b]) * kHop);
+        }
+        s_rowbase[r] = base;
+      }
+      __syncwarp();
+      for (int ps = 0; ps < P.passes; ++ps)
+        for (int c = 0; c < kChunks; ++c, ++cseq) {
+          const uint32_t st = cseq % kRawStages, use = cseq / kRawStages;
+          mbar_wait(smem_u32(&bars->raw_empty[st]), (use & 1) ^ 1, P.status, 301);
+          const uint32_t fw = smem_u32(s_raw + (size_t)st * kRawStageBytes);
+          const uint32_t mw = fw + kTileM * kRawPitch * 4;
+          // forward window: xp[base + 16c + i], i = 0..19 (5 x 16 B per row; taps n = 16c+1 .. 16c+16 are i = 1..16)
+#pragma unroll 4
+          for (int it = 0; it < (kTileM * 5) / 32; ++it) {
+            const int idx = it * 32 + lane, r = idx / 5, pc = idx - r * 5;
+            const int32_t base = s_rowbase[r];
+            const float* src = P.xp + (base >= 0 ? (int64_t)base + kKC * c + 4 * pc : 0);
+            cp_async16(fw + (uint32_t)(r * kRawPitch + 4 * pc) * 4u, src, base >= 0 ? 16u : 0u);
+          }
+          // mirrored window: xp[base + 1008 - 16c + i], i = 0..15 (taps N-n are i = 15-j)
+#pragma unroll 4
+          for (int it = 0; it < (kTileM * 4) / 32; ++it) {
+            const int idx = it * 32 + lane, r = idx >> 2, pc = idx & 3;
+            const int32_t base = s_rowbase[r];
+            const float* src = P.xp + (base >= 0 ? (int64_t)base + (kNfft - kKC) - kKC * c + 4 * pc : 0);
+            cp_async16(mw + (uint32_t)(r * kRawPitch + 4 * pc) * 4u, src, base >= 0 ? 16u : 0u);
+          }
+          cp_async_arrive(smem_u32(&bars->raw_full[st]));
+        }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  } else if (warp >= kWarpConv0 && warp < kWarpEpi0) {
+    // ===== converters: fold + TF32 split -> TMEM A operand =====
+    const int set = (warp - kWarpConv0) >> 2;          // which A stage this warp feeds
+    const int q = warp & 3;                            // TMEM lane quarter
+    const int r = q * 32 + lane;                       // frame row of this thread
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    uint32_t cseq = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+      for (int ps = 0; ps < P.passes; ++ps)
+        for (int c = 0; c < kChunks; ++c, ++cseq) {
+          if ((int)(cseq & 1) != set) continue;
+          const uint32_t st = cseq % kRawStages, use = cseq / kRawStages;
+          mbar_wait(smem_u32(&bars->raw_full[st]), use & 1, P.status, 401);
+          const float4* fw = reinterpret_cast<const float4*>(s_raw + (size_t)st * kRawStageBytes + (size_t)r * kRawPitch * 4);
+          const float4* mw = reinterpret_cast<const float4*>(s_raw + (size_t)st * kRawStageBytes + (size_t)(kTileM + r) * kRawPitch * 4);
+          float f[20], m[16];
+#pragma unroll
+          for (int i = 0; i < 5; ++i) { const float4 v = fw[i]; f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w; }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { const float4 v = mw[i]; m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w; }
+          uint32_t hi[16], lo[16];
+          const uint32_t as = cseq & 1, ause = cseq >> 1;
+          const uint32_t a_base = tmem + lane_addr + kColA + as * 64;
+          // E = f[n] + f[N-n]
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float e = f[1 + j] + m[15 - j];
+            const uint32_t h = tf32_bits(__float_as_uint(e));
+            hi[j] = h;
+            lo[j] = tf32_bits(__float_as_uint(e - __uint_as_float(h)));
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&bars->raw_empty[st]));   // staged rows are now in registers
+          mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
+          tc_fence_after();
+          tmem_st16(a_base + 0, hi);
+          tmem_st16(a_base + 16, lo);
+          // O = f[n] - f[N-n]
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float o = f[1 + j] - m[15 - j];
+            const uint32_t h = tf32_bits(__float_as_uint(o));
+            hi[j] = h;
+            lo[j] = tf32_bits(__float_as_uint(o - __uint_as_float(h)));
+          }
+          tmem_st16(a_base + 32, hi);
+          tmem_st16(a_base + 48, lo);
+          tmem_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
+        }
+  } else if (warp >= kWarpEpi0) {
+    // ===== epilogue: power -> sparse mel -> log(clamp) -> / norm =====
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    uint32_t pseq = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int64_t g = (int64_t)tile * kTileM + r;
+      bool valid = g < total_frames;
+      float* orow = nullptr;
+      if (valid) {
+        const int b = find_clip(P.frame_off, P.B, g);
+        const int t = (int)(g - P.frame_off[b]);
+        valid = t < P.Tmax;
+        orow = P.out + ((int64_t)b * P.Tmax + t) * P.n_mels;
+      }
+      int cur = 0;               // filter index of acc_lo
+      float acc_lo = 0.f, acc_hi = 0.f;
+      auto emit = [&](int mth, float v) {
+        if (valid && mth < P.n_mels) {
+          float y = logf(fmaxf(v, P.clamp));
+          if (P.norms) y = y / s_norm[mth];
+          orow[mth] = y;
+        }
+      };
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
+        tc_fence_after();
+        for (int c0 = 0; c0 < nb; c0 += 16) {
+          uint32_t re[16], im[16];
+          tmem_ld16(tmem + lane_addr + c0, re);
+          tmem_ld16(tmem + lane_addr + kColIm + c0, im);
+          tmem_wait_ld();
+          if (P.dbg_reim && valid) {
+            float* d = P.dbg_reim + g * (2 * P.nbt) + ps * nb + c0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { d[j] = __uint_as_float(re[j]); d[P.nbt + j] = __uint_as_float(im[j]); }
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float4 tb = s_tab[ps * nb + c0 + j];
+            const int flo = __float_as_int(tb.z);
+            while (cur < flo) { emit(cur, acc_lo); acc_lo = acc_hi; acc_hi = 0.f; ++cur; }
+            const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
+            float pw = fmaf(a, a, bq * bq);
+            if (P.power_is_1) pw = sqrtf(pw);
+            acc_lo = fmaf(tb.x, pw, acc_lo);
+            acc_hi = fmaf(tb.y, pw, acc_hi);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
+      }
+      // flush the running filters and the (empty) ones above them
+      for (; cur < P.n_mels; ++cur) { emit(cur, acc_lo); acc_lo = acc_hi; acc_hi = 0.f; }
+    }
+  }
+
+  // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWarpTmem) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTmemCols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_simt: plain CUDA-core fp32 implementation of the same maths (cross-check kernel)
+// ------------------------------------------------------------------------------------------
+constexpr int kSimtFrames = 8;
+constexpr int kSimtThreads = 256;
+
+__global__ void __launch_bounds__(kSimtThreads) k_simt(const float* __restrict__ xp, int64_t Lp,
+                                                       const int64_t* __restrict__ frame_off,
+                                                       int B, int Tmax, float* __restrict__ out,
+                                                       const float* __restrict__ cosf_, const float* __restrict__ sinf__,
+                                                       const float* __restrict__ fb, const float* __restrict__ norms,
+                                                       int nbt, int n_mels, float clamp, int power_is_1) {
+  extern __shared__ float sm[];
+  float* sE = sm;                                  // [F][512]
+  float* sO = sE + kSimtFrames * kKfold;           // [F][512]
+  float* sP = sO + kSimtFrames * kKfold;           // [F][nbt]
+  __shared__ int64_t s_out[kSimtFrames];
+  const int64_t total = frame_off[B];
+  const int64_t g0 = (int64_t)blockIdx.x * kSimtFrames;
+  for (int f = 0; f < kSimtFrames; ++f) {
+    const int64_t g = g0 + f;
+    int64_t base = -1, oidx = -1;
+    if (g < total) {
+      const int b = find_clip(frame_off, B, g);
+      const int64_t t = g - frame_off[b];
+      base = (int64_t)b * Lp + t * kHop;
+      if (t < Tmax) oidx = ((int64_t)b * Tmax + t) * n_mels;
+    }
+    if (threadIdx.x == 0) s_out[f] = oidx;
+    for (int kap = threadIdx.x; kap < kKfold; kap += kSimtThreads) {
+      const int n = kap + 1;
+      const float a = base >= 0 ? xp[base + n] : 0.f, c = base >= 0 ? xp[base + kNfft - n] : 0.f;
+      sE[f * kKfold + kap] = a + c;
+      sO[f * kKfold + kap] = a - c;
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nbt; i += kSimtThreads) {
+    float re[kSimtFrames], im[kSimtFrames];
+#pragma unroll
+    for (int f = 0; f < kSimtFrames; ++f) re[f] = im[f] = 0.f;
+    for (int kap = 0; kap < kKfold; ++kap) {
+      const float c = cosf_[(size_t)kap * nbt + i], s = sinf__[(size_t)kap * nbt + i];
+#pragma unroll
+      for (int f = 0; f < kSimtFrames; ++f) {
+        re[f] = fmaf(sE[f * kKfold + kap], c, re[f]);
+        im[f] = fmaf(sO[f * kKfold + kap], s, im[f]);
+      }
+    }
+#pragma unroll
+    for (int f = 0; f < kSimtFrames; ++f) {
+      float pw = fmaf(re[f], re[f], im[f] * im[f]);
+      if (power_is_1) pw = sqrtf(pw);
+      sP[f * nbt + i] = pw;
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < kSimtFrames * n_mels; idx += kSimtThreads) {
+    const int f = idx / n_mels, m = idx - f * n_mels;
+    if (s_out[f] < 0) continue;
+    float acc = 0.f;
+    for (int i = 0; i < nbt; ++i) acc = fmaf(sP[f * nbt + i], fb[(size_t)i * n_mels + m], acc);
+    float y = logf(fmaxf(acc, clamp));
+    if (norms) y = y / norms[m];
+    out[s_out[f] + m] = y;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_stats: per-channel sum / sumsq / count of log-mel over valid frames (fp64 accumulation)
+// ------------------------------------------------------------------------------------------
+constexpr int kStatRows = 8;
+
+__global__ void __launch_bounds__(kMaxMels* kStatRows) k_stats(const float* __restrict__ logmel,
+                                                               const int32_t* __restrict__ n_frames, int B, int Tmax,
+                                                               int n_mels, double* __restrict__ acc) {
+  __shared__ double s_sum[kStatRows][kMaxMels], s_sq[kStatRows][kMaxMels];
+  const int c = threadIdx.x, ry = threadIdx.y;
+  double sum = 0.0, sq = 0.0;
+  long long cnt = 0;
+  // segments = clips; rows beyond n_frames[b] are padding and are skipped
+  for (int b = blockIdx.y; b < B; b += gridDim.y) {
+    const int T = min(n_frames[b], Tmax);
+    const float* base = logmel + (int64_t)b * Tmax * n_mels;
+    for (int t = blockIdx.x * kStatRows + ry; t < T; t += gridDim.x * kStatRows) {
+      if (c < n_mels) {
+        const double v = (double)base[(int64_t)t * n_mels + c];
+        sum += v;
+        sq += v * v;
+      }
+      if (c == 0) ++cnt;
+    }
+  }
+  s_sum[ry][c] = sum;
+  s_sq[ry][c] = sq;
+  // frame count: warp-shuffle reduction over the lanes that counted, one atomic per warp
+  unsigned long long wc = (unsigned long long)cnt;
+  for (int d = 16; d > 0; d >>= 1) wc += __shfl_down_sync(0xffffffffu, wc, d);
+  __syncthreads();
+  if (ry == 0 && c < n_mels) {
+    double a = 0.0, q = 0.0;
+#pragma unroll
+    for (int y = 0; y < kStatRows; ++y) { a += s_sum[y][c]; q += s_sq[y][c]; }
+    atomicAdd(acc + c, a);
+    atomicAdd(acc + n_mels + c, q);
+  }
+  if (((threadIdx.y * blockDim.x + threadIdx.x) & 31) == 0 && wc) atomicAdd(acc + 2 * n_mels, (double)wc);
+}
+
+// ------------------------------------------------------------------------------------------
+// host: launches
+// ------------------------------------------------------------------------------------------
+namespace {
+
+size_t logmel_smem_bytes(const ttts_mel_plan* p) {
+  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawStages * kRawStageBytes + (size_t)p->nbt * sizeof(float4) +
+             kMaxMels * 4 + kTileM * 4 + sizeof(LogmelBarriers) + 16;
+  return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
+}
+
+enum class Impl { Tcgen05, Simt };
+
+int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, const int64_t* lengths, int32_t B,
+                 int64_t Lmax, int32_t Tmax, float* out, int32_t* n_frames_user, uint8_t* mask, void* ws_ptr,
+                 size_t ws_bytes, void* stream_, Impl impl, float* dbg_reim) {
+  g_launches = 0;
+  if (!p || !wav || !out || !ws_ptr) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || Lmax <= 0 || Tmax <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d Lmax=%lld Tmax=%d)", B, (long long)Lmax, Tmax);
+  if (row_stride < Lmax) return fail(TTTS_MEL_EINVAL, "row_stride %lld < Lmax %lld", (long long)row_stride, (long long)Lmax);
+  if (ttts_mel_frames(p, Lmax) < 0) return TTTS_MEL_EINVAL;
+  Workspace w = carve(p, ws_ptr, B, Lmax);
+  if (ws_bytes < w.bytes) return fail(TTTS_MEL_ENOMEM, "workspace %zu < %zu bytes", ws_bytes, w.bytes);
+  if ((int64_t)B * w.Lp >= (int64_t)1 << 31) return fail(TTTS_MEL_EINVAL, "batch too large for 32-bit row offsets: split it");
+  cudaStream_t stream = (cudaStream_t)stream_;
+
+  CUDA_TRY(cudaMemsetAsync(w.status, 0, 256, stream));
+  k_prep<<<1, 1024, 0, stream>>>(lengths, B, Lmax, p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.status);
+  ++g_launches;
+  const int vec_ok = (row_stride % 4 == 0) && (((uintptr_t)wav & 15) == 0);
+  {
+    const int64_t vecs = (w.Lp + 3) / 4;
+    dim3 grid((unsigned)((vecs + 255) / 256 > 4096 ? 4096 : (vecs + 255) / 256), (unsigned)B);
+    k_pad<<<grid, 256, 0, stream>>>(wav, row_stride, lengths, Lmax, p->cfg.pad, w.xp, w.Lp, vec_ok);
+    ++g_launches;
+  }
+  if (lengths) CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)B * Tmax * p->cfg.n_mels * sizeof(float), stream));
+  if (mask) {
+    k_mask<<<p->num_sms * 4, 256, 0, stream>>>(w.n_frames, B, Tmax, mask);
+    ++g_launches;
+  }
+  if (impl == Impl::Tcgen05) {
+    LogmelParams P{};
+    P.xp = w.xp; P.Lp = w.Lp; P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
+    P.out = out; P.basis = p->d_basis; P.meltab = p->d_meltab; P.norms = p->d_norms;
+    P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
+    P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim;
+    const size_t smem = logmel_smem_bytes(p);
+    static thread_local size_t configured = 0;
+    if (configured < smem) {
+      CUDA_TRY(cudaFuncSetAttribute(k_logmel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured = smem;
+    }
+    k_logmel<<<p->num_sms, kThreads, smem, stream>>>(P);
+    ++g_launches;
+  } else {
+    const int64_t Tall = ttts_mel_frames(p, Lmax);
+    const int64_t max_frames = (int64_t)B * Tall;
+    const unsigned blocks = (unsigned)((max_frames + kSimtFrames - 1) / kSimtFrames);
+    const size_t smem = (size_t)(2 * kSimtFrames * kKfold + kSimtFrames * p->nbt) * 4;
+    static thread_local size_t configured = 0;
+    if (configured < smem) {
+      CUDA_TRY(cudaFuncSetAttribute(k_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured = smem;
+    }
+    k_simt<<<blocks, kSimtThreads, smem, stream>>>(w.xp, w.Lp, w.frame_off, B, Tmax, out, p->d_cosf, p->d_sinf, p->d_fb,
+                                                  p->d_norms, p->nbt, p->cfg.n_mels, p->cfg.clamp, p->cfg.power == 1.0f);
+    ++g_launches;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return TTTS_MEL_OK;
+}
+
+}  // namespace
+
+extern "C" int ttts_mel_forward(const ttts_mel_plan* p, const float* wav, int64_t row_stride, const int64_t* lengths,
+                                int32_t B, int64_t Lmax, int32_t Tmax, float* out, int32_t* n_frames, uint8_t* mask,
+                                void* ws, size_t ws_bytes, void* stream) {
+  return forward_impl(p, wav, row_stride, lengths, B, Lmax, Tmax, out, n_frames, mask, ws, ws_bytes, stream,
+                      Impl::Tcgen05, nullptr);
+}
+
+extern "C" int ttts_mel_forward_simt(const ttts_mel_plan* p, const float* wav, int64_t row_stride,
+                                     const int64_t* lengths, int32_t B, int64_t Lmax, int32_t Tmax, float* out,
+                                     int32_t* n_frames, uint8_t* mask, void* ws, size_t ws_bytes, void* stream) {
+  return forward_impl(p, wav, row_stride, lengths, B, Lmax, Tmax, out, n_frames, mask, ws, ws_bytes, stream,
+                      Impl::Simt, nullptr);
+}
+
+extern "C" int ttts_mel_forward_debug(const ttts_mel_plan* p, const float* wav, int64_t row_stride,
+                                      const int64_t* lengths, int32_t B, int64_t Lmax, int32_t Tmax, float* out,
+                                      int32_t* n_frames, uint8_t* mask, void* ws, size_t ws_bytes, void* stream,
+                                      float* reim_out) {
+  if (!reim_out) return fail(TTTS_MEL_EINVAL, "reim_out_dev is null");
+  return forward_impl(p, wav, row_stride, lengths, B, Lmax, Tmax, out, n_frames, mask, ws, ws_bytes, stream,
+                      Impl::Tcgen05, reim_out);
+}
+
+extern "C" int ttts_mel_status(const void* ws, void* stream) {
+  if (!ws) return fail(TTTS_MEL_EINVAL, "null workspace");
+  cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(TTTS_MEL_ECUDA, "stream sync: %s", cudaGetErrorString(e));
+  int32_t code = 0;
+  CUDA_TRY(cudaMemcpy(&code, ws, sizeof(code), cudaMemcpyDeviceToHost));
+  if (code == 0) return TTTS_MEL_OK;
+  if (code == 1) return fail(TTTS_MEL_EDEVICE, "a clip length is <= pad, shorter than the window, or > Lmax");
+  if (code == 2) return fail(TTTS_MEL_EDEVICE, "Tmax is smaller than a clip's frame count");
+  return fail(TTTS_MEL_EDEVICE, "pipeline wait timed out (code %d)", code);
+}
+
+extern "C" int ttts_mel_stats_accumulate(const ttts_mel_plan* p, const float* logmel, const int32_t* n_frames,
+                                         int32_t B, int32_t Tmax, double* acc, void* stream) {
+  if (!p || !logmel || !n_frames || !acc) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || Tmax <= 0) return fail(TTTS_MEL_EINVAL, "empty batch");
+  dim3 block(kMaxMels, kStatRows);
+  int gx = (Tmax + kStatRows * 8 - 1) / (kStatRows * 8);
+  if (gx < 1) gx = 1;
+  if (gx > 64) gx = 64;
+  int gy = B < 64 ? B : 64;
+  k_stats<<<dim3(gx, gy), block, 0, (cudaStream_t)stream>>>(logmel, n_frames, B, Tmax, p->cfg.n_mels, acc);
+  g_launches = 1;
+  CUDA_TRY(cudaGetLastError());
+  return TTTS_MEL_OK;
+}

@@ -1,0 +1,300 @@
+"""Host-side mirror of the reference's log-mel modules, running on the sm_100a library.
+
+Drop-in for (same class names, constructor arguments, attributes, call semantics and error
+behaviour; file:line in /root/reference):
+
+* ``TorchMelSpectrogram``      ttts/utils/utils.py:486-522           (V1, 22.05 kHz / 80 mel / power 2)
+* ``MelSpectrogramFeatures``   ttts/vocoder/feature_extractors.py:73-99 (V2, 24 kHz / 100 mel / power 1)
+* ``dvae_wav_to_mel``          ttts/vqvae/xtts_dvae.py:28-49
+* ``make_pad_mask``            ttts/utils/utils.py:77-103
+
+plus one additive keyword, ``forward(wav, lengths=...)``, for ragged batches: every clip is
+reflect-padded at its own end (the reference processes one clip per call,
+ttts/prepare/mel_extract.py:15-27) and the result follows the loaders' collate contract
+(zero-padded mels + integer lengths + ``make_pad_mask``, ttts/gpt/dataset.py:95-130).
+
+PyTorch is used for device memory and streams only; the arithmetic is in ``libttts_mel.so``.
+CUDA tensors only -- there is no CPU path here.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+import os
+from typing import Optional, Sequence, Tuple, Union
+
+import torch
+from torch import nn
+
+from . import _cabi
+from .filterbank import analysis_window, melscale_fbanks
+
+DEFAULT_MEL_NORM_FILE = os.path.join(os.path.dirname(os.path.realpath(__file__)), "data", "mel_norms.pth")
+
+
+def make_pad_mask(lengths: torch.Tensor, max_len: int = 0) -> torch.Tensor:
+    """mask[b, t] = t >= lengths[b]  (True = padded part), as ttts/utils/utils.py:77-103."""
+    batch_size = lengths.size(0)
+    max_len = max_len if max_len > 0 else int(lengths.max().item())
+    seq_range = torch.arange(0, max_len, dtype=torch.int64, device=lengths.device)
+    return seq_range.unsqueeze(0).expand(batch_size, max_len) >= lengths.unsqueeze(-1)
+
+
+class MelPlan:
+    """One immutable device plan (folded basis, mel table) + the forward call.  One per device."""
+
+    def __init__(self, *, sample_rate: int, n_fft: int, hop_length: int, win_length: Optional[int],
+                 n_mels: int, f_min: float, f_max: Optional[float], power: float, norm: Optional[str],
+                 mel_scale: str = "htk", normalized: bool = False, clamp: float = 1e-5,
+                 center: bool = True, pre_pad: int = 0, device: Union[str, torch.device, int] = "cuda"):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("MelPlan needs a CUDA device (sm_100a); there is no CPU fallback")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.n_fft, self.hop, self.n_mels = int(n_fft), int(hop_length), int(n_mels)
+        self.pad = self.n_fft // 2 if center else int(pre_pad)
+        self.power, self.clamp = float(power), float(clamp)
+        f_max = float(f_max) if f_max is not None else float(sample_rate // 2)
+        self.fb = melscale_fbanks(self.n_fft // 2 + 1, float(f_min), f_max, self.n_mels, int(sample_rate),
+                                  norm, mel_scale).contiguous()
+        self.window = analysis_window(self.n_fft, win_length).contiguous()
+        spec_scale = 1.0
+        if normalized:      # torchaudio functional.py:139-140: spec_f /= window.pow(2).sum().sqrt()
+            spec_scale = 1.0 / math.sqrt(float(self.window.pow(2.0).sum()))
+        cfg = _cabi.MelConfig(self.n_fft, self.hop, self.n_mels, self.pad, self.power, self.clamp, spec_scale)
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().ttts_mel_plan_create(ctypes.byref(cfg), self.fb.data_ptr(),
+                                                         self.window.data_ptr(), ctypes.byref(handle)))
+        self._h = handle
+        self.first_bin = int(_cabi.lib().ttts_mel_first_bin(self._h))
+        self.num_bins = int(_cabi.lib().ttts_mel_num_bins(self._h))
+        self.live_bins = int(_cabi.lib().ttts_mel_live_bins(self._h))
+        self.last_launches = 0
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                _cabi.lib().ttts_mel_plan_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    def set_norms(self, norms: Optional[torch.Tensor]) -> None:
+        with torch.cuda.device(self.device):
+            if norms is None:
+                _cabi.check(_cabi.lib().ttts_mel_plan_set_norms(self._h, None))
+                return
+            host = norms.detach().to("cpu", torch.float32).contiguous()
+            if host.numel() != self.n_mels:
+                raise ValueError(f"mel_norms has {host.numel()} entries, expected {self.n_mels}")
+            # the plan is read by kernels already in flight on this device's streams
+            torch.cuda.synchronize(self.device)
+            _cabi.check(_cabi.lib().ttts_mel_plan_set_norms(self._h, host.data_ptr()))
+
+    def frames(self, length: int) -> int:
+        """torch.stft frame count; raises like F.pad(mode='reflect') when the clip is too short."""
+        if length <= self.pad or length + 2 * self.pad < self.n_fft:
+            raise RuntimeError(
+                f"Argument #4: Padding size should be less than the corresponding input dimension, but got: "
+                f"padding ({self.pad}, {self.pad}) at dimension 1 of input of length {length}")
+        return 1 + (length + 2 * self.pad - self.n_fft) // self.hop
+
+    def forward(self, wav: torch.Tensor, lengths: Optional[torch.Tensor] = None, *, want_mask: bool = False,
+                impl: str = "tcgen05", debug_reim: bool = False, t_max: Optional[int] = None):
+        """wav [B, L] fp32 CUDA (last dim contiguous).  Returns (mel_btc [B, T, n_mels] fp32,
+        n_frames [B] int32, mask [B, T] uint8 | None[, reim])."""
+        if wav.device != self.device:
+            raise RuntimeError(f"input on {wav.device}, plan on {self.device}")
+        if wav.dtype != torch.float32 or wav.dim() != 2:
+            raise RuntimeError("MelPlan.forward expects a 2-D float32 tensor")
+        if wav.stride(1) != 1 or wav.stride(0) < wav.shape[1]:
+            wav = wav.contiguous()
+        B, Lmax = int(wav.shape[0]), int(wav.shape[1])
+        if B == 0:
+            raise RuntimeError("empty batch")
+        T = self.frames(Lmax) if t_max is None else int(t_max)
+        lib = _cabi.lib()
+        len_dev = None
+        if lengths is not None:
+            len_dev = lengths.to(device=self.device, dtype=torch.int64).contiguous()
+            if len_dev.numel() != B:
+                raise ValueError("lengths must have one entry per clip")
+        with torch.cuda.device(self.device):
+            ws_bytes = int(lib.ttts_mel_workspace_bytes(self._h, B, Lmax))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
+            out = torch.empty((B, T, self.n_mels), dtype=torch.float32, device=self.device)
+            n_frames = torch.empty((B,), dtype=torch.int32, device=self.device)
+            mask = torch.empty((B, T), dtype=torch.uint8, device=self.device) if want_mask else None
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            args = [self._h, wav.data_ptr(), int(wav.stride(0)), len_dev.data_ptr() if len_dev is not None else None,
+                    B, Lmax, T, out.data_ptr(), n_frames.data_ptr(), mask.data_ptr() if mask is not None else None,
+                    ws.data_ptr(), ws_bytes, stream]
+            reim = None
+            if debug_reim:
+                total = B * self.frames(Lmax)
+                reim = torch.zeros((total, 2 * self.num_bins), dtype=torch.float32, device=self.device)
+                _cabi.check(lib.ttts_mel_forward_debug(*args, reim.data_ptr()))
+            elif impl == "tcgen05":
+                _cabi.check(lib.ttts_mel_forward(*args))
+            elif impl == "simt":
+                _cabi.check(lib.ttts_mel_forward_simt(*args))
+            else:
+                raise ValueError(f"unknown impl {impl!r}")
+            self.last_launches = int(lib.ttts_mel_last_launch_count())
+            self._last_ws = ws
+        if debug_reim:
+            return out, n_frames, mask, reim
+        return out, n_frames, mask
+
+    def status(self) -> None:
+        """Synchronise and raise if the last forward reported a device-side error."""
+        ws = getattr(self, "_last_ws", None)
+        if ws is None:
+            return
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            _cabi.check(_cabi.lib().ttts_mel_status(ws.data_ptr(), stream))
+
+    def stats_accumulate(self, logmel_btc: torch.Tensor, n_frames: torch.Tensor, acc: torch.Tensor) -> None:
+        """acc[2*n_mels+1] (fp64, device) += [sum | sumsq | count] of un-normalised log-mel."""
+        assert logmel_btc.is_contiguous() and logmel_btc.dtype == torch.float32
+        assert acc.dtype == torch.float64 and acc.numel() == 2 * self.n_mels + 1 and acc.is_contiguous()
+        nf = n_frames.to(device=self.device, dtype=torch.int32).contiguous()
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            _cabi.check(_cabi.lib().ttts_mel_stats_accumulate(
+                self._h, logmel_btc.data_ptr(), nf.data_ptr(), int(logmel_btc.shape[0]), int(logmel_btc.shape[1]),
+                acc.data_ptr(), stream))
+
+
+class _MelModuleBase(nn.Module):
+    """Shared forward logic of the two reference modules."""
+
+    def _plan_kwargs(self) -> dict:
+        raise NotImplementedError
+
+    def _norms(self) -> Optional[torch.Tensor]:
+        return None
+
+    def _plan_for(self, device: torch.device) -> MelPlan:
+        plans = self.__dict__.setdefault("_plans", {})
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+        plan = plans.get(key)
+        if plan is None:
+            plan = MelPlan(device=torch.device(*key), **self._plan_kwargs())
+            plans[key] = plan
+            plan._norms_key = None
+        norms = self._norms()
+        nkey = None if norms is None else (id(norms), norms._version, norms.data_ptr())
+        if nkey != plan._norms_key:
+            plan.set_norms(norms)
+            plan._norms_key = nkey
+        return plan
+
+    def _run(self, inp: torch.Tensor, lengths=None, impl: str = "tcgen05"):
+        if len(inp.shape) == 3:   # squeeze the channel dimension (mono), utils.py:510-511
+            inp = inp.squeeze(1)
+        assert len(inp.shape) == 2
+        if not inp.is_cuda:
+            raise RuntimeError(f"{type(self).__name__} (xtts_b200) runs on CUDA sm_100a only; got a {inp.device} tensor "
+                               "and there is no CPU fallback")
+        if inp.dtype == torch.float64:
+            raise RuntimeError("expected scalar type Float but found Double")   # torch.stft's complaint
+        if inp.dtype != torch.float32:
+            inp = inp.float()       # fp16/bf16 promote to an fp32 result in the reference too
+        plan = self._plan_for(inp.device)
+        if lengths is None:
+            mel, _, _ = plan.forward(inp, impl=impl)
+            return mel.transpose(1, 2)          # [B, n_mels, T] view with the reference's strides
+        lens = torch.as_tensor(lengths)
+        if lens.dim() != 1 or lens.numel() != inp.shape[0]:
+            raise ValueError("lengths must be 1-D with one entry per clip")
+        if not lens.is_cuda:
+            lmin, lmax = int(lens.min()), int(lens.max())
+            if lmax > inp.shape[1]:
+                raise ValueError(f"a length ({lmax}) exceeds the padded width {inp.shape[1]}")
+            plan.frames(lmin)                    # raises for clips too short to reflect-pad
+            t_max = plan.frames(lmax)
+        else:
+            t_max = None
+        mel, n_frames, mask = plan.forward(inp, lens, want_mask=True, impl=impl, t_max=t_max)
+        return mel.transpose(1, 2), n_frames.to(torch.int64), mask.bool()
+
+
+class TorchMelSpectrogram(_MelModuleBase):
+    """ttts/utils/utils.py:486-522 on the B200 library."""
+
+    def __init__(self, filter_length=1024, hop_length=256, win_length=1024, n_mel_channels=80, mel_fmin=0,
+                 mel_fmax=8000, sampling_rate=22050, normalize=False, mel_norm_file=DEFAULT_MEL_NORM_FILE):
+        super().__init__()
+        self.filter_length = filter_length
+        self.hop_length = hop_length
+        self.win_length = win_length
+        self.n_mel_channels = n_mel_channels
+        self.mel_fmin = mel_fmin
+        self.mel_fmax = mel_fmax
+        self.sampling_rate = sampling_rate
+        self.normalize = normalize
+        self.mel_stft = None            # the reference keeps a torchaudio transform here; nothing to keep
+        self.mel_norm_file = mel_norm_file
+        if self.mel_norm_file is not None:
+            self.mel_norms = torch.load(self.mel_norm_file)
+        else:
+            self.mel_norms = None
+
+    def _plan_kwargs(self) -> dict:
+        return dict(sample_rate=self.sampling_rate, n_fft=self.filter_length, hop_length=self.hop_length,
+                    win_length=self.win_length, n_mels=self.n_mel_channels, f_min=self.mel_fmin,
+                    f_max=self.mel_fmax, power=2.0, norm="slaney", mel_scale="htk",
+                    normalized=bool(self.normalize), clamp=1e-5, center=True)
+
+    def _norms(self):
+        return self.mel_norms
+
+    def forward(self, inp, lengths=None):
+        return self._run(inp, lengths)
+
+
+class MelSpectrogramFeatures(_MelModuleBase):
+    """ttts/vocoder/feature_extractors.py:73-99 (+ safe_log, ttts/vocoder/modules.py:194-205)."""
+
+    def __init__(self, sample_rate=24000, n_fft=1024, hop_length=256, win_length=None, n_mels=100, mel_fmin=0,
+                 mel_fmax=None, normalize=False, padding="center"):
+        super().__init__()
+        if padding not in ["center", "same"]:
+            raise ValueError("Padding must be 'center' or 'same'.")
+        self.padding = padding
+        self.sample_rate, self.n_fft, self.hop_length = sample_rate, n_fft, hop_length
+        self.win_length = win_length if win_length is not None else n_fft
+        self.n_mels, self.mel_fmin, self.mel_fmax, self.normalize = n_mels, mel_fmin, mel_fmax, normalize
+
+    def _plan_kwargs(self) -> dict:
+        same = self.padding == "same"
+        return dict(sample_rate=self.sample_rate, n_fft=self.n_fft, hop_length=self.hop_length,
+                    win_length=self.win_length, n_mels=self.n_mels, f_min=self.mel_fmin, f_max=self.mel_fmax,
+                    power=1.0, norm=None, mel_scale="htk", normalized=bool(self.normalize), clamp=1e-7,
+                    center=not same, pre_pad=(self.win_length - self.hop_length) // 2 if same else 0)
+
+    def forward(self, audio, lengths=None, **kwargs):
+        return self._run(audio, lengths)
+
+
+_DVAE_MODULES = {}
+
+
+def dvae_wav_to_mel(wav, mel_norms_file="../experiments/clips_mel_norms.pth", mel_norms=None,
+                    device=torch.device("cuda")):
+    """ttts/vqvae/xtts_dvae.py:28-49 (the reference rebuilds its transform every call; the plan is cached)."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("dvae_wav_to_mel (xtts_b200) runs on CUDA only; there is no CPU fallback")
+    mod = _DVAE_MODULES.get("v1")
+    if mod is None:
+        mod = _DVAE_MODULES["v1"] = TorchMelSpectrogram(mel_norm_file=None)
+    if mel_norms is None:
+        mel_norms = torch.load(mel_norms_file, map_location=device)
+    mod.mel_norms = mel_norms
+    return mod(wav.to(device))
