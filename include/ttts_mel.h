@@ -128,6 +128,13 @@ int ttts_mel_stats_accumulate(const ttts_mel_plan* plan, const float* logmel_dev
 /* Kernel launches the last ttts_mel_forward* call on this thread enqueued (for bench accounting). */
 int32_t ttts_mel_last_launch_count(void);
 
+/* Measurement hooks: when enabled, every ttts_mel_forward records a library-owned CUDA event pair
+ * around the fused log-mel kernel on the launch stream (up to max_calls calls; 0 disables).
+ * ttts_mel_profile_collect synchronises the device, writes the per-call kernel durations in ms and
+ * returns how many were written (then restarts the ring). */
+int ttts_mel_profile_enable(int32_t max_calls);
+int ttts_mel_profile_collect(float* ms_out, int32_t capacity);
+
 const char* ttts_mel_last_error(void);
 const char* ttts_mel_version(void);
 

@@ -63,6 +63,14 @@ constexpr int kWarpEpi0 = 12;          // 4 epilogue warps: 12..15
 thread_local char g_err[512] = "";
 thread_local int g_launches = 0;
 
+// optional per-call timing of the hot kernel (library-owned CUDA event pairs, see ttts_mel_profile_*)
+struct ProfileRing {
+  cudaEvent_t* start = nullptr;
+  cudaEvent_t* stop = nullptr;
+  int capacity = 0, count = 0;
+};
+ProfileRing g_prof;
+
 int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -945,7 +953,10 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
       CUDA_TRY(cudaFuncSetAttribute(k_logmel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       configured = smem;
     }
+    const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
+    if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
     k_logmel<<<p->num_sms, kThreads, smem, stream>>>(P);
+    if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
     ++g_launches;
   } else {
     const int64_t Tall = ttts_mel_frames(p, Lmax);
@@ -1015,4 +1026,30 @@ extern "C" int ttts_mel_stats_accumulate(const ttts_mel_plan* p, const float* lo
   g_launches = 1;
   CUDA_TRY(cudaGetLastError());
   return TTTS_MEL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// profiling hooks: CUDA-event duration of k_logmel alone, per forward call, on the launch stream
+// ------------------------------------------------------------------------------------------
+extern "C" int ttts_mel_profile_enable(int32_t max_calls) {
+  for (int i = 0; i < g_prof.capacity; ++i) { cudaEventDestroy(g_prof.start[i]); cudaEventDestroy(g_prof.stop[i]); }
+  delete[] g_prof.start; delete[] g_prof.stop;
+  g_prof = ProfileRing();
+  if (max_calls <= 0) return TTTS_MEL_OK;
+  g_prof.start = new cudaEvent_t[max_calls];
+  g_prof.stop = new cudaEvent_t[max_calls];
+  for (int i = 0; i < max_calls; ++i) {
+    CUDA_TRY(cudaEventCreate(&g_prof.start[i]));
+    CUDA_TRY(cudaEventCreate(&g_prof.stop[i]));
+  }
+  g_prof.capacity = max_calls;
+  return TTTS_MEL_OK;
+}
+
+extern "C" int ttts_mel_profile_collect(float* ms_out, int32_t capacity) {
+  CUDA_TRY(cudaDeviceSynchronize());
+  const int n = g_prof.count < capacity ? g_prof.count : capacity;
+  for (int i = 0; i < n; ++i) CUDA_TRY(cudaEventElapsedTime(&ms_out[i], g_prof.start[i], g_prof.stop[i]));
+  g_prof.count = 0;
+  return n;
 }
