@@ -127,8 +127,8 @@ def test_dft_stage_vs_fp64(dev):
         re = _np(reim[b * T:(b + 1) * T, :live])
         im = _np(reim[b * T:(b + 1) * T, nbt:nbt + live])
         scale = np.abs(st.re).max()
-        assert np.abs(re - st.re[:, k0:k0 + live]).max() <= 2e-6 * scale
-        assert np.abs(im + st.im[:, k0:k0 + live]).max() <= 2e-6 * scale
+        assert np.abs(re - st.re[:, k0:k0 + live]).max() <= 6e-6 * scale      # fp32 TMEM accumulation, 3xTF32 products
+        assert np.abs(im + st.im[:, k0:k0 + live]).max() <= 6e-6 * scale
 
 
 def test_simt_crosscheck_full_size(dev, v1):

@@ -45,9 +45,11 @@ constexpr int kChunks = kKfold / kKC;  // 32 chunks per pass
 constexpr int kKSteps = kKfold / kKStep;  // 64 basis stages per pass
 constexpr int kNBMax = 192;            // bins per pass (accumulator columns: re | im)
 constexpr int kBStages = 5;            // basis ring depth (one k-step each)
-constexpr int kRawStages = 4;          // raw-audio ring depth (one chunk each)
+constexpr int kConvWarps = 8;           // converter warps (2 sets x 4 TMEM lane quarters)
+constexpr int kConvDepth = 2;           // raw-audio stages per converter warp (= 4 chunks ahead overall)
 constexpr int kRawPitch = 20;          // floats per staged row (80 B: conflict-free row-per-thread LDS.128)
-constexpr int kRawStageBytes = 2 * kTileM * kRawPitch * 4;   // forward window + mirrored window
+constexpr int kConvStageBytes = 2 * 32 * kRawPitch * 4;      // 32 rows x (forward window + mirrored window)
+constexpr int kRawBytes = kConvWarps * kConvDepth * kConvStageBytes;
 constexpr int kTmemCols = 512;
 constexpr int kColIm = kNBMax;         // accumulator columns: re [0,NB), im [192,192+NB)
 constexpr int kColA = 2 * kNBMax;      // A ring: 2 stages x 64 columns (E_hi,E_lo,O_hi,O_lo x 16)
@@ -56,7 +58,7 @@ constexpr int kMaxMels = 128;
 constexpr long long kTimeoutCycles = 4000000000LL;
 
 // warp roles of k_logmel
-constexpr int kWarpTma = 0, kWarpMma = 1, kWarpTmem = 2, kWarpLoad = 3;
+constexpr int kWarpTma = 0, kWarpMma = 1, kWarpTmem = 2;   // warp 3 is spare
 constexpr int kWarpConv0 = 4;          // 8 converter warps: 4..11   (warp % 4 == TMEM lane quarter)
 constexpr int kWarpEpi0 = 12;          // 4 epilogue warps: 12..15
 
@@ -363,9 +365,6 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
-}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -525,9 +524,28 @@ struct LogmelParams {
   float* dbg_reim;            // optional [total_frames][2*nbt]
 };
 
+// Running state of the sparse mel contraction: every bin feeds filters (cur, cur+1) only.
+struct MelRun { float lo, hi; int cur; };
+
+// Close filters cur .. upto-1: y = log(max(sum, clamp)) [/ norm].  Kept out of line: it runs ~n_mels
+// times per frame while the bin loop around it is unrolled 16x (instruction-cache footprint).
+__device__ __noinline__ MelRun mel_flush(MelRun r, int upto, float* __restrict__ orow, int n_mels, float clamp,
+                                         const float* s_norm) {
+  while (r.cur < upto) {
+    if (orow && r.cur < n_mels) {
+      float y = logf(fmaxf(r.lo, clamp));
+      if (s_norm) y = y / s_norm[r.cur];
+      orow[r.cur] = y;
+    }
+    r.lo = r.hi;
+    r.hi = 0.f;
+    ++r.cur;
+  }
+  return r;
+}
+
 struct __align__(8) LogmelBarriers {
   uint64_t b_full[kBStages], b_empty[kBStages];
-  uint64_t raw_full[kRawStages], raw_empty[kRawStages];
   uint64_t a_full[2], a_empty[2];
   uint64_t acc_full, acc_empty;
 };
@@ -539,10 +557,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   const uint32_t b_stage_bytes = (uint32_t)nb * 128u;       // 4 arrays x 2 k-halves x nb rows x 16 B
   uint8_t* s_b = smem;                                       // basis ring
   uint8_t* s_raw = s_b + (size_t)kBStages * b_stage_bytes;   // raw audio ring
-  float4* s_tab = reinterpret_cast<float4*>(s_raw + (size_t)kRawStages * kRawStageBytes);
+  float4* s_tab = reinterpret_cast<float4*>(s_raw + (size_t)kRawBytes);
   float* s_norm = reinterpret_cast<float*>(s_tab + P.nbt);
-  int32_t* s_rowbase = reinterpret_cast<int32_t*>(s_norm + kMaxMels);
-  LogmelBarriers* bars = reinterpret_cast<LogmelBarriers*>(s_rowbase + kTileM);
+  LogmelBarriers* bars = reinterpret_cast<LogmelBarriers*>(s_norm + kMaxMels);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -554,7 +571,6 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   for (int i = threadIdx.x; i < P.n_mels; i += kThreads) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStages; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
-    for (int i = 0; i < kRawStages; ++i) { mbar_init(smem_u32(&bars->raw_full[i]), 32); mbar_init(smem_u32(&bars->raw_empty[i]), 4); }
     for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
     mbar_init(smem_u32(&bars->acc_full), 1);
     mbar_init(smem_u32(&bars->acc_empty), 4);
@@ -628,64 +644,84 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         }
     }
     __syncwarp();
-  } else if (warp == kWarpLoad) {
-    // ===== raw-audio loader: cp.async gathers of the hop windows of 128 frames =====
-    uint32_t cseq = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      __syncwarp();
-#pragma unroll
-      for (int i = 0; i < kTileM / 32; ++i) {
-        const int r = lane + 32 * i;
-        const int64_t g = (int64_t)tile * kTileM + r;
-        int32_t base = -1;
+  } else if (warp >= kWarpConv0 && warp < kWarpEpi0) {
+    // ===== converters: gather own rows (cp.async) -> fold + TF32 split -> TMEM A operand =====
+    // Warp (q, set) owns frame rows 32q..32q+31 of the tile for the chunks c == set (mod 2).  It stages
+    // exactly the rows it later reads, so the only synchronisation of the raw-audio ring is
+    // cp.async.wait_group + __syncwarp: no loader warp, no mbarriers on this leg.
+    const int cw = warp - kWarpConv0;
+    const int set = cw >> 2;                           // which A stage (and chunk parity) this warp feeds
+    const int q = warp & 3;                            // TMEM lane quarter
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    uint8_t* my_raw = s_raw + (size_t)cw * kConvDepth * kConvStageBytes;
+    const int fj = lane & 7, fr = lane >> 3;           // forward window: 8 lanes per row (5 active), rows fr + 4k
+    const int mj = lane & 3, mr = lane >> 2;           // mirrored window: 4 lanes per row, rows mr + 8k
+
+    // issue cursor (runs kConvDepth chunks ahead of the consume cursor)
+    int i_tile = blockIdx.x, i_ps = 0, i_c = set;
+    int32_t off_f[8], off_m[4];
+    auto load_row_offsets = [&](int tile) {
+      int32_t base = -1;
+      if (tile < num_tiles) {
+        const int64_t g = (int64_t)tile * kTileM + q * 32 + lane;
         if (g < total_frames) {
           const int b = find_clip(P.frame_off, P.B, g);
           base = (int32_t)((int64_t)b * P.Lp + (g - P.frame_off[b]) * kHop);
         }
-        s_rowbase[r] = base;
       }
-      __syncwarp();
-      for (int ps = 0; ps < P.passes; ++ps)
-        for (int c = 0; c < kChunks; ++c, ++cseq) {
-          const uint32_t st = cseq % kRawStages, use = cseq / kRawStages;
-          mbar_wait(smem_u32(&bars->raw_empty[st]), (use & 1) ^ 1, P.status, 301);
-          const uint32_t fw = smem_u32(s_raw + (size_t)st * kRawStageBytes);
-          const uint32_t mw = fw + kTileM * kRawPitch * 4;
-          // forward window: xp[base + 16c + i], i = 0..19 (5 x 16 B per row; taps n = 16c+1 .. 16c+16 are i = 1..16)
-#pragma unroll 4
-          for (int it = 0; it < (kTileM * 5) / 32; ++it) {
-            const int idx = it * 32 + lane, r = idx / 5, pc = idx - r * 5;
-            const int32_t base = s_rowbase[r];
-            const float* src = P.xp + (base >= 0 ? (int64_t)base + kKC * c + 4 * pc : 0);
-            cp_async16(fw + (uint32_t)(r * kRawPitch + 4 * pc) * 4u, src, base >= 0 ? 16u : 0u);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int32_t v = __shfl_sync(0xffffffffu, base, fr + 4 * k);
+        off_f[k] = v >= 0 ? v + 4 * fj : -1;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int32_t v = __shfl_sync(0xffffffffu, base, mr + 8 * k);
+        off_m[k] = v >= 0 ? v + (kNfft - kKC) + 4 * mj : -1;
+      }
+    };
+    auto issue = [&](uint32_t stage) {
+      if (i_tile < num_tiles) {
+        const uint32_t fw = smem_u32(my_raw + (size_t)stage * kConvStageBytes);
+        const uint32_t mw = fw + 32 * kRawPitch * 4;
+        const int adv = kKC * i_c;
+        // forward window: xp[row + 16c + i], i = 0..19 (taps n = 16c+1 .. 16c+16 are i = 1..16)
+        if (fj < 5) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const bool ok = off_f[k] >= 0;
+            cp_async16(fw + (uint32_t)((fr + 4 * k) * kRawPitch + 4 * fj) * 4u, P.xp + (ok ? off_f[k] + adv : 0), ok ? 16u : 0u);
           }
-          // mirrored window: xp[base + 1008 - 16c + i], i = 0..15 (taps N-n are i = 15-j)
-#pragma unroll 4
-          for (int it = 0; it < (kTileM * 4) / 32; ++it) {
-            const int idx = it * 32 + lane, r = idx >> 2, pc = idx & 3;
-            const int32_t base = s_rowbase[r];
-            const float* src = P.xp + (base >= 0 ? (int64_t)base + (kNfft - kKC) - kKC * c + 4 * pc : 0);
-            cp_async16(mw + (uint32_t)(r * kRawPitch + 4 * pc) * 4u, src, base >= 0 ? 16u : 0u);
-          }
-          cp_async_arrive(smem_u32(&bars->raw_full[st]));
         }
-    }
-    asm volatile("cp.async.wait_all;" ::: "memory");
-  } else if (warp >= kWarpConv0 && warp < kWarpEpi0) {
-    // ===== converters: fold + TF32 split -> TMEM A operand =====
-    const int set = (warp - kWarpConv0) >> 2;          // which A stage this warp feeds
-    const int q = warp & 3;                            // TMEM lane quarter
-    const int r = q * 32 + lane;                       // frame row of this thread
-    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    uint32_t cseq = 0;
+        // mirrored window: xp[row + 1008 - 16c + i], i = 0..15 (tap N-n is i = 15-j)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const bool ok = off_m[k] >= 0;
+          cp_async16(mw + (uint32_t)((mr + 8 * k) * kRawPitch + 4 * mj) * 4u, P.xp + (ok ? off_m[k] - adv : 0), ok ? 16u : 0u);
+        }
+        // advance the cursor over (tile, pass, chunk of my parity)
+        i_c += 2;
+        if (i_c >= kChunks) {
+          i_c = set;
+          if (++i_ps >= P.passes) { i_ps = 0; i_tile += gridDim.x; load_row_offsets(i_tile); }
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");   // empty groups keep the wait_group count uniform
+    };
+
+    load_row_offsets(i_tile);
+#pragma unroll
+    for (int d = 0; d < kConvDepth; ++d) issue(d);
+
+    uint32_t cseq = set, mine = 0;                     // cseq: global chunk counter (A-stage phases); mine: my chunk counter
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
       for (int ps = 0; ps < P.passes; ++ps)
-        for (int c = 0; c < kChunks; ++c, ++cseq) {
-          if ((int)(cseq & 1) != set) continue;
-          const uint32_t st = cseq % kRawStages, use = cseq / kRawStages;
-          mbar_wait(smem_u32(&bars->raw_full[st]), use & 1, P.status, 401);
-          const float4* fw = reinterpret_cast<const float4*>(s_raw + (size_t)st * kRawStageBytes + (size_t)r * kRawPitch * 4);
-          const float4* mw = reinterpret_cast<const float4*>(s_raw + (size_t)st * kRawStageBytes + (size_t)(kTileM + r) * kRawPitch * 4);
+        for (int c = set; c < kChunks; c += 2, cseq += 2, ++mine) {
+          const uint32_t stage = mine % kConvDepth;
+          asm volatile("cp.async.wait_group %0;" ::"n"(kConvDepth - 1) : "memory");
+          __syncwarp();
+          const float4* fw = reinterpret_cast<const float4*>(my_raw + (size_t)stage * kConvStageBytes + (size_t)lane * kRawPitch * 4);
+          const float4* mw = fw + 32 * kRawPitch / 4;
           float f[20], m[16];
 #pragma unroll
           for (int i = 0; i < 5; ++i) { const float4 v = fw[i]; f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w; }
@@ -702,8 +738,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
             hi[j] = h;
             lo[j] = tf32_bits(__float_as_uint(e - __uint_as_float(h)));
           }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&bars->raw_empty[st]));   // staged rows are now in registers
+          __syncwarp();                                  // every lane has its row in registers: the stage can be refilled
+          issue(stage);
           mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
           tc_fence_after();
           tmem_st16(a_base + 0, hi);
@@ -723,6 +759,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
         }
+    asm volatile("cp.async.wait_all;" ::: "memory");
   } else if (warp >= kWarpEpi0) {
     // ===== epilogue: power -> sparse mel -> log(clamp) -> / norm =====
     const int q = warp & 3;
@@ -739,15 +776,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         valid = t < P.Tmax;
         orow = P.out + ((int64_t)b * P.Tmax + t) * P.n_mels;
       }
-      int cur = 0;               // filter index of acc_lo
-      float acc_lo = 0.f, acc_hi = 0.f;
-      auto emit = [&](int mth, float v) {
-        if (valid && mth < P.n_mels) {
-          float y = logf(fmaxf(v, P.clamp));
-          if (P.norms) y = y / s_norm[mth];
-          orow[mth] = y;
-        }
-      };
+      MelRun run{0.f, 0.f, 0};   // running pair of adjacent filters (cur, cur+1)
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
         tc_fence_after();
@@ -765,12 +794,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           for (int j = 0; j < 16; ++j) {
             const float4 tb = s_tab[ps * nb + c0 + j];
             const int flo = __float_as_int(tb.z);
-            while (cur < flo) { emit(cur, acc_lo); acc_lo = acc_hi; acc_hi = 0.f; ++cur; }
+            if (run.cur < flo) run = mel_flush(run, flo, valid ? orow : nullptr, P.n_mels, P.clamp, P.norms ? s_norm : nullptr);
             const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
             float pw = fmaf(a, a, bq * bq);
             if (P.power_is_1) pw = sqrtf(pw);
-            acc_lo = fmaf(tb.x, pw, acc_lo);
-            acc_hi = fmaf(tb.y, pw, acc_hi);
+            run.lo = fmaf(tb.x, pw, run.lo);
+            run.hi = fmaf(tb.y, pw, run.hi);
           }
         }
         tc_fence_before();
@@ -778,7 +807,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
       }
       // flush the running filters and the (empty) ones above them
-      for (; cur < P.n_mels; ++cur) { emit(cur, acc_lo); acc_lo = acc_hi; acc_hi = 0.f; }
+      mel_flush(run, P.n_mels, valid ? orow : nullptr, P.n_mels, P.clamp, P.norms ? s_norm : nullptr);
     }
   }
 
@@ -906,8 +935,8 @@ __global__ void __launch_bounds__(kMaxMels* kStatRows) k_stats(const float* __re
 namespace {
 
 size_t logmel_smem_bytes(const ttts_mel_plan* p) {
-  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawStages * kRawStageBytes + (size_t)p->nbt * sizeof(float4) +
-             kMaxMels * 4 + kTileM * 4 + sizeof(LogmelBarriers) + 16;
+  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawBytes + (size_t)p->nbt * sizeof(float4) +
+             kMaxMels * 4 + sizeof(LogmelBarriers) + 16;
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
 }
 
