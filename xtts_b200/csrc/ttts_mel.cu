@@ -44,7 +44,7 @@ constexpr int kKStep = 8;              // K of one tcgen05.mma kind::tf32
 constexpr int kChunks = kKfold / kKC;  // 32 chunks per pass
 constexpr int kKSteps = kKfold / kKStep;  // 64 basis stages per pass
 constexpr int kNBMax = 192;            // bins per pass (accumulator columns: re | im)
-constexpr int kBStages = 5;            // basis ring depth (one k-step each)
+constexpr int kBStages = 4;            // basis ring depth (one k-step each)
 constexpr int kConvWarps = 8;           // converter warps (2 sets x 4 TMEM lane quarters)
 constexpr int kConvDepth = 2;           // raw-audio stages per converter warp (= 4 chunks ahead overall)
 constexpr int kRawPitch = 20;          // floats per staged row (80 B: conflict-free row-per-thread LDS.128)
@@ -101,7 +101,8 @@ struct ttts_mel_plan {
   int nb = 0;          // bins per pass (multiple of 16, <= 192)
   int nbt = 0;         // passes * nb
   float* d_basis = nullptr;    // [passes][64 k-steps][4 arrays][2 k-halves][nb][4] fp32 (TF32-exact values)
-  float4* d_meltab = nullptr;  // [nbt] {w_lo, w_hi, bits(filter_lo), 0}
+  float2* d_melw = nullptr;    // [nbt] weights of bin i into the running filter pair (cur, cur+1)
+  unsigned long long* d_meladv = nullptr;  // [nbt/16] 4 bits per bin: filters closed before the bin
   float* d_norms = nullptr;    // [n_mels] or nullptr
   float* d_cosf = nullptr;     // [512][nbt] plain fp32 folded basis for k_simt
   float* d_sinf = nullptr;
@@ -162,11 +163,13 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   const int nb = p->nb, nbt = p->nbt;
 
   // sparse mel table: every bin feeds at most two ADJACENT filters (triangular filterbanks)
-  std::vector<float4> tab(nbt);
+  std::vector<float2> melw(nbt);
+  std::vector<unsigned long long> meladv(nbt / 16, 0ull);
   std::vector<float> fbl((size_t)nbt * nm, 0.f);
   int cur = 0;
   for (int i = 0; i < nbt; ++i) {
     float wlo = 0.f, whi = 0.f;
+    int adv = 0;
     if (i < p->n_live) {
       const float* row = fb + (size_t)(kmin + i) * nm;
       int first = -1, last = -1;
@@ -175,19 +178,18 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
         if (row[m] != 0.f) { if (first < 0) first = m; last = m; }
       }
       if (first >= 0) {
-        if (last - first > 1 || first < cur) {
+        if (last - first > 1 || first < cur || first - cur > 15) {
           delete p;
           return fail(TTTS_MEL_EINVAL, "filterbank row %d is not two adjacent, non-decreasing filters", kmin + i);
         }
+        adv = first - cur;
         cur = first;
         wlo = row[first];
         whi = (last > first) ? row[last] : 0.f;
       }
     }
-    float4 t;
-    t.x = wlo; t.y = whi; t.z = 0.f; t.w = 0.f;
-    memcpy(&t.z, &cur, 4);
-    tab[i] = t;
+    melw[i] = make_float2(wlo, whi);
+    meladv[i >> 4] |= (unsigned long long)adv << (4 * (i & 15));
   }
 
   // folded, windowed basis.  kappa = n-1 for n = 1..512;  the n = 512 tap appears once, so it
@@ -239,7 +241,8 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
     if (e == cudaSuccess) e = cudaMemcpy(*dptr, src, bytes, cudaMemcpyHostToDevice);
   };
   up((void**)&p->d_basis, img.data(), img.size() * 4);
-  up((void**)&p->d_meltab, tab.data(), tab.size() * sizeof(float4));
+  up((void**)&p->d_melw, melw.data(), melw.size() * sizeof(float2));
+  up((void**)&p->d_meladv, meladv.data(), meladv.size() * sizeof(unsigned long long));
   up((void**)&p->d_cosf, cosf.data(), cosf.size() * 4);
   up((void**)&p->d_sinf, sinf_.data(), sinf_.size() * 4);
   up((void**)&p->d_fb, fbl.data(), fbl.size() * 4);
@@ -266,7 +269,7 @@ extern "C" int ttts_mel_plan_set_norms(ttts_mel_plan* p, const float* norms) {
 
 extern "C" void ttts_mel_plan_destroy(ttts_mel_plan* p) {
   if (!p) return;
-  cudaFree(p->d_basis); cudaFree(p->d_meltab); cudaFree(p->d_norms);
+  cudaFree(p->d_basis); cudaFree(p->d_melw); cudaFree(p->d_meladv); cudaFree(p->d_norms);
   cudaFree(p->d_cosf); cudaFree(p->d_sinf); cudaFree(p->d_fb);
   delete p;
 }
@@ -515,7 +518,8 @@ struct LogmelParams {
   int Tmax;
   float* out;                 // [B][Tmax][n_mels]
   const float* basis;         // tiled stage images
-  const float4* meltab;       // [nbt]
+  const float2* melw;         // [nbt]
+  const unsigned long long* meladv;   // [nbt/16]
   const float* norms;         // [n_mels] or null
   int passes, nb, nbt, n_mels;
   float clamp;
@@ -523,26 +527,6 @@ struct LogmelParams {
   int32_t* status;
   float* dbg_reim;            // optional [total_frames][2*nbt]
 };
-
-// Running state of the sparse mel contraction: every bin feeds filters (cur, cur+1) only.
-struct MelRun { float lo, hi; int cur; };
-
-// Close filters cur .. upto-1: y = log(max(sum, clamp)) [/ norm].  Kept out of line: it runs ~n_mels
-// times per frame while the bin loop around it is unrolled 16x (instruction-cache footprint).
-__device__ __noinline__ MelRun mel_flush(MelRun r, int upto, float* __restrict__ orow, int n_mels, float clamp,
-                                         const float* s_norm) {
-  while (r.cur < upto) {
-    if (orow && r.cur < n_mels) {
-      float y = logf(fmaxf(r.lo, clamp));
-      if (s_norm) y = y / s_norm[r.cur];
-      orow[r.cur] = y;
-    }
-    r.lo = r.hi;
-    r.hi = 0.f;
-    ++r.cur;
-  }
-  return r;
-}
 
 struct __align__(8) LogmelBarriers {
   uint64_t b_full[kBStages], b_empty[kBStages];
@@ -557,9 +541,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   const uint32_t b_stage_bytes = (uint32_t)nb * 128u;       // 4 arrays x 2 k-halves x nb rows x 16 B
   uint8_t* s_b = smem;                                       // basis ring
   uint8_t* s_raw = s_b + (size_t)kBStages * b_stage_bytes;   // raw audio ring
-  float4* s_tab = reinterpret_cast<float4*>(s_raw + (size_t)kRawBytes);
-  float* s_norm = reinterpret_cast<float*>(s_tab + P.nbt);
-  LogmelBarriers* bars = reinterpret_cast<LogmelBarriers*>(s_norm + kMaxMels);
+  float2* s_melw = reinterpret_cast<float2*>(s_raw + (size_t)kRawBytes);
+  unsigned long long* s_adv = reinterpret_cast<unsigned long long*>(s_melw + P.nbt);
+  float* s_norm = reinterpret_cast<float*>(s_adv + P.nbt / 16);      // [kMaxMels] mel_norms (or 1)
+  float* s_park = s_norm + kMaxMels;                                 // [128][n_mels+1] raw mel sums of the tile
+  const int park_pitch = P.n_mels + 1;
+  LogmelBarriers* bars = reinterpret_cast<LogmelBarriers*>(s_park + ((kTileM * park_pitch + 1) & ~1));
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -567,7 +554,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   const int num_tiles = (int)((total_frames + kTileM - 1) / kTileM);
 
   // ---- one-time setup
-  for (int i = threadIdx.x; i < P.nbt; i += kThreads) s_tab[i] = P.meltab[i];
+  for (int i = threadIdx.x; i < P.nbt; i += kThreads) s_melw[i] = P.melw[i];
+  for (int i = threadIdx.x; i < P.nbt / 16; i += kThreads) s_adv[i] = P.meladv[i];
   for (int i = threadIdx.x; i < P.n_mels; i += kThreads) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStages; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
@@ -776,7 +764,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         valid = t < P.Tmax;
         orow = P.out + ((int64_t)b * P.Tmax + t) * P.n_mels;
       }
-      MelRun run{0.f, 0.f, 0};   // running pair of adjacent filters (cur, cur+1)
+      // Sparse mel contraction: every bin feeds the running pair of adjacent filters (cur, cur+1); the
+      // host table says how many filters close before each bin.  Closed filters are parked as raw sums
+      // in shared memory and turned into log-mel in a coalesced pass once the tile is finished, so the
+      // accumulator drain below is branch-light and free of transcendental code.
+      float run_lo = 0.f, run_hi = 0.f;
+      int cur = 0;
+      float* prow = s_park + r * park_pitch;
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
         tc_fence_after();
@@ -784,7 +778,19 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           uint32_t re[16], im[16];
           tmem_ld16(tmem + lane_addr + c0, re);
           tmem_ld16(tmem + lane_addr + kColIm + c0, im);
+          const unsigned long long advw = s_adv[(ps * nb + c0) >> 4];
+          float2 w[16];
+          {
+            const float4* wp = reinterpret_cast<const float4*>(s_melw + ps * nb + c0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float4 v = wp[j]; w[2 * j] = make_float2(v.x, v.y); w[2 * j + 1] = make_float2(v.z, v.w); }
+          }
           tmem_wait_ld();
+          if (c0 + 16 >= nb) {           // accumulators of this pass are in registers: hand TMEM back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
+          }
           if (P.dbg_reim && valid) {
             float* d = P.dbg_reim + g * (2 * P.nbt) + ps * nb + c0;
 #pragma unroll
@@ -792,22 +798,39 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           }
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const float4 tb = s_tab[ps * nb + c0 + j];
-            const int flo = __float_as_int(tb.z);
-            if (run.cur < flo) run = mel_flush(run, flo, valid ? orow : nullptr, P.n_mels, P.clamp, P.norms ? s_norm : nullptr);
+            uint32_t adv = (uint32_t)(advw >> (4 * j)) & 15u;
+            if (adv) {
+              do {
+                if (cur < P.n_mels) prow[cur] = run_lo;
+                run_lo = run_hi; run_hi = 0.f; ++cur;
+              } while (--adv);
+            }
             const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
             float pw = fmaf(a, a, bq * bq);
             if (P.power_is_1) pw = sqrtf(pw);
-            run.lo = fmaf(tb.x, pw, run.lo);
-            run.hi = fmaf(tb.y, pw, run.hi);
+            run_lo = fmaf(w[j].x, pw, run_lo);
+            run_hi = fmaf(w[j].y, pw, run_hi);
           }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
       }
-      // flush the running filters and the (empty) ones above them
-      mel_flush(run, P.n_mels, valid ? orow : nullptr, P.n_mels, P.clamp, P.norms ? s_norm : nullptr);
+      // close the running filters and the (empty) ones above them
+      for (; cur < P.n_mels; ++cur) {
+        prow[cur] = run_lo;
+        run_lo = run_hi; run_hi = 0.f;
+      }
+      // raw mel sums -> log(max(., clamp)) / norm, one coalesced output row at a time
+      __syncwarp();
+#pragma unroll 4
+      for (int rr = 0; rr < 32; ++rr) {
+        const unsigned long long pr = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr);
+        const int ok = __shfl_sync(0xffffffffu, (int)valid, rr);
+        if (!ok) continue;
+        float* rowp = reinterpret_cast<float*>((uintptr_t)pr);
+        const float* parked = s_park + (q * 32 + rr) * park_pitch;
+        for (int mth = lane; mth < P.n_mels; mth += 32)
+          rowp[mth] = logf(fmaxf(parked[mth], P.clamp)) / s_norm[mth];   // true division, as the reference
+      }
+      __syncwarp();
     }
   }
 
@@ -935,8 +958,8 @@ __global__ void __launch_bounds__(kMaxMels* kStatRows) k_stats(const float* __re
 namespace {
 
 size_t logmel_smem_bytes(const ttts_mel_plan* p) {
-  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawBytes + (size_t)p->nbt * sizeof(float4) +
-             kMaxMels * 4 + sizeof(LogmelBarriers) + 16;
+  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawBytes + (size_t)p->nbt * sizeof(float2) + (size_t)p->nbt / 2 +
+             kMaxMels * 4 + (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + sizeof(LogmelBarriers) + 16;
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
 }
 
@@ -973,7 +996,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   if (impl == Impl::Tcgen05) {
     LogmelParams P{};
     P.xp = w.xp; P.Lp = w.Lp; P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
-    P.out = out; P.basis = p->d_basis; P.meltab = p->d_meltab; P.norms = p->d_norms;
+    P.out = out; P.basis = p->d_basis; P.melw = p->d_melw; P.meladv = p->d_meladv; P.norms = p->d_norms;
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
     P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim;
     const size_t smem = logmel_smem_bytes(p);
