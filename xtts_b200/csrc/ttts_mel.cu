@@ -52,7 +52,8 @@ constexpr int kConvStageBytes = 2 * 32 * kRawPitch * 4;      // 32 rows x (forwa
 constexpr int kRawBytes = kConvWarps * kConvDepth * kConvStageBytes;
 constexpr int kTmemCols = 512;
 constexpr int kColIm = kNBMax;         // accumulator columns: re [0,NB), im [192,192+NB)
-constexpr int kColA = 2 * kNBMax;      // A ring: 2 stages x 64 columns (E_hi,E_lo,O_hi,O_lo x 16)
+constexpr int kColA = 2 * kNBMax;      // A ring: 4 stages x 32 columns (E_hi,E_lo,O_hi,O_lo x 8 = one k-step)
+constexpr int kAStages = 4;
 constexpr int kThreads = 512;
 constexpr int kMaxMels = 128;
 constexpr long long kTimeoutCycles = 4000000000LL;
@@ -381,12 +382,10 @@ __device__ __forceinline__ void mma_tf32_ts(uint32_t d, uint32_t a, uint64_t bde
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
       ::"r"(d), "r"(a), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
 }
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* v) {
   asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-        "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
   asm volatile(
@@ -399,14 +398,14 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// K-major, SWIZZLE_NONE shared-memory matrix descriptor (sm_100 format, version 1)
-__device__ __forceinline__ uint64_t make_bdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;   // descriptor version
-  return d;                 // base_offset 0, lbo_mode 0, layout_type 0 (no swizzle)
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred) : "r"(0xffffffffu));
+  return pred;
 }
 
 // round-to-nearest TF32 of an fp32 bit pattern
@@ -530,7 +529,7 @@ struct LogmelParams {
 
 struct __align__(8) LogmelBarriers {
   uint64_t b_full[kBStages], b_empty[kBStages];
-  uint64_t a_full[2], a_empty[2];
+  uint64_t a_full[kAStages], a_empty[kAStages];
   uint64_t acc_full, acc_empty;
 };
 
@@ -559,7 +558,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   for (int i = threadIdx.x; i < P.n_mels; i += kThreads) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStages; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
+    for (int i = 0; i < kAStages; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
     mbar_init(smem_u32(&bars->acc_full), 1);
     mbar_init(smem_u32(&bars->acc_empty), 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -590,33 +589,35 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
     }
     __syncwarp();
   } else if (warp == kWarpMma) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nb >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
-      const uint32_t lbo = (uint32_t)nb * 16u, sbo = 128u, arr_bytes = (uint32_t)nb * 32u;
-      const uint32_t d_re = tmem, d_im = tmem + kColIm;
-      uint32_t bseq = 0, cseq = 0, pseq = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
-        for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-          mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
-          tc_fence_after();
-          for (int c = 0; c < kChunks; ++c, ++cseq) {
-            const uint32_t as = cseq & 1, ause = cseq >> 1;
-            mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
-            tc_fence_after();
-            const uint32_t a_base = tmem + kColA + as * 64;
+    // ===== MMA issuer: the whole warp stays converged (waits are warp-uniform), one elected lane issues =====
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nb >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+    // K-major SWIZZLE_NONE descriptors: high word is constant (SBO = 128 B, version 1), low word = addr>>4 | LBO>>4 << 16
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);
+    const uint32_t desc_lo0 = (((uint32_t)nb * 16u) >> 4) << 16;
+    const uint32_t arr16 = ((uint32_t)nb * 32u) >> 4;           // one operand array, in 16 B units
+    const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
+    const uint32_t d_re = tmem, d_im = tmem + kColIm;
+    uint32_t bseq = 0, cseq = 0, pseq = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        for (int c = 0; c < kChunks; ++c, ++cseq) {
 #pragma unroll
-            for (int kk = 0; kk < kKC / kKStep; ++kk, ++bseq) {
-              const uint32_t st = bseq % kBStages, use = bseq / kBStages;
-              mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
-              tc_fence_after();
-              const uint32_t sb_addr = smem_u32(s_b + (size_t)st * b_stage_bytes);
-              const uint64_t c_hi = make_bdesc(sb_addr, lbo, sbo);
-              const uint64_t c_lo = make_bdesc(sb_addr + arr_bytes, lbo, sbo);
-              const uint64_t s_hi = make_bdesc(sb_addr + 2 * arr_bytes, lbo, sbo);
-              const uint64_t s_lo = make_bdesc(sb_addr + 3 * arr_bytes, lbo, sbo);
-              const uint32_t e_hi = a_base + 0 + kk * kKStep, e_lo = a_base + 16 + kk * kKStep;
-              const uint32_t o_hi = a_base + 32 + kk * kKStep, o_lo = a_base + 48 + kk * kKStep;
+          for (int kk = 0; kk < kKC / kKStep; ++kk, ++bseq) {
+            // A stage: chunks of parity p use stages 2p (first k-step) and 2p+1 (second k-step)
+            const uint32_t as = 2 * (cseq & 1) + kk, ause = cseq >> 1;
+            const uint32_t st = bseq % kBStages, use = bseq / kBStages;
+            mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+            mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+            tc_fence_after();
+            if (elect_one_sync()) {
+              const uint32_t a_base = tmem + kColA + as * 32;
+              const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
+              const uint64_t c_hi = ((uint64_t)desc_hi << 32) | lo;
+              const uint64_t c_lo = ((uint64_t)desc_hi << 32) | (lo + arr16);
+              const uint64_t s_hi = ((uint64_t)desc_hi << 32) | (lo + 2 * arr16);
+              const uint64_t s_lo = ((uint64_t)desc_hi << 32) | (lo + 3 * arr16);
+              const uint32_t e_hi = a_base, e_lo = a_base + 8, o_hi = a_base + 16, o_lo = a_base + 24;
               const uint32_t first = (c == 0 && kk == 0) ? 0u : 1u;
               mma_tf32_ts(d_re, e_lo, c_hi, idesc, first);   // small terms first
               mma_tf32_ts(d_re, e_hi, c_lo, idesc, 1u);
@@ -625,13 +626,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
               mma_tf32_ts(d_im, o_hi, s_lo, idesc, 1u);
               mma_tf32_ts(d_im, o_hi, s_hi, idesc, 1u);
               tc_commit(smem_u32(&bars->b_empty[st]));       // basis stage free once these MMAs retire
+              tc_commit(smem_u32(&bars->a_empty[as]));       // A stage free
+              if (c == kChunks - 1 && kk == kKC / kKStep - 1)
+                tc_commit(smem_u32(&bars->acc_full));        // accumulators of this pass complete
             }
-            tc_commit(smem_u32(&bars->a_empty[as]));         // A stage free
+            __syncwarp();
           }
-          tc_commit(smem_u32(&bars->acc_full));              // accumulators of this pass complete
         }
-    }
-    __syncwarp();
+      }
   } else if (warp >= kWarpConv0 && warp < kWarpEpi0) {
     // ===== converters: gather own rows (cp.async) -> fold + TF32 split -> TMEM A operand =====
     // Warp (q, set) owns frame rows 32q..32q+31 of the tile for the chunks c == set (mod 2).  It stages
@@ -715,37 +717,33 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           for (int i = 0; i < 5; ++i) { const float4 v = fw[i]; f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w; }
 #pragma unroll
           for (int i = 0; i < 4; ++i) { const float4 v = mw[i]; m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w; }
-          uint32_t hi[16], lo[16];
-          const uint32_t as = cseq & 1, ause = cseq >> 1;
-          const uint32_t a_base = tmem + lane_addr + kColA + as * 64;
-          // E = f[n] + f[N-n]
+          uint32_t ehi[16], elo[16], ohi[16], olo[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const float e = f[1 + j] + m[15 - j];
-            const uint32_t h = tf32_bits(__float_as_uint(e));
-            hi[j] = h;
-            lo[j] = tf32_bits(__float_as_uint(e - __uint_as_float(h)));
+            const float e = f[1 + j] + m[15 - j];          // E = f[n] + f[N-n]
+            const float o = f[1 + j] - m[15 - j];          // O = f[n] - f[N-n]
+            const uint32_t he = tf32_bits(__float_as_uint(e)), ho = tf32_bits(__float_as_uint(o));
+            ehi[j] = he; elo[j] = tf32_bits(__float_as_uint(e - __uint_as_float(he)));
+            ohi[j] = ho; olo[j] = tf32_bits(__float_as_uint(o - __uint_as_float(ho)));
           }
           __syncwarp();                                  // every lane has its row in registers: the stage can be refilled
           issue(stage);
-          mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
-          tc_fence_after();
-          tmem_st16(a_base + 0, hi);
-          tmem_st16(a_base + 16, lo);
-          // O = f[n] - f[N-n]
+          const uint32_t ause = cseq >> 1;               // == mine: how often this set's A stages were used
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float o = f[1 + j] - m[15 - j];
-            const uint32_t h = tf32_bits(__float_as_uint(o));
-            hi[j] = h;
-            lo[j] = tf32_bits(__float_as_uint(o - __uint_as_float(h)));
+          for (int h = 0; h < 2; ++h) {                  // one TMEM stage per k-step (8 kappa)
+            const uint32_t as = 2 * set + h;
+            const uint32_t a_base = tmem + lane_addr + kColA + as * 32;
+            mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
+            tc_fence_after();
+            tmem_st8(a_base + 0, ehi + 8 * h);
+            tmem_st8(a_base + 8, elo + 8 * h);
+            tmem_st8(a_base + 16, ohi + 8 * h);
+            tmem_st8(a_base + 24, olo + 8 * h);
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
           }
-          tmem_st16(a_base + 32, hi);
-          tmem_st16(a_base + 48, lo);
-          tmem_wait_st();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
         }
     asm volatile("cp.async.wait_all;" ::: "memory");
   } else if (warp >= kWarpEpi0) {
