@@ -533,6 +533,21 @@ struct __align__(8) LogmelBarriers {
   uint64_t acc_full, acc_empty;
 };
 
+// Running state of the sparse mel contraction: every bin feeds the adjacent filter pair (cur, cur+1).
+struct MelRun { float lo, hi; int cur; };
+
+// Close `adv` filters: park their raw sums in the tile's shared-memory row.  Out of line on purpose: it runs
+// ~n_mels times per frame, while the bin loop that calls it is unrolled 16x and must stay small enough for
+// the instruction cache.
+__device__ __noinline__ MelRun mel_advance(MelRun r, uint32_t adv, float* prow, int n_mels) {
+  do {
+    if (r.cur < n_mels) prow[r.cur] = r.lo;
+    r.lo = r.hi; r.hi = 0.f; ++r.cur;
+  } while (--adv);
+  return r;
+}
+
+template <bool kPower1, bool kDebug>
 __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];
   // ---- carve shared memory
@@ -766,8 +781,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
       // host table says how many filters close before each bin.  Closed filters are parked as raw sums
       // in shared memory and turned into log-mel in a coalesced pass once the tile is finished, so the
       // accumulator drain below is branch-light and free of transcendental code.
-      float run_lo = 0.f, run_hi = 0.f;
-      int cur = 0;
+      MelRun run{0.f, 0.f, 0};
       float* prow = s_park + r * park_pitch;
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
@@ -789,33 +803,28 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
           }
-          if (P.dbg_reim && valid) {
-            float* d = P.dbg_reim + g * (2 * P.nbt) + ps * nb + c0;
+          if (kDebug) {
+            if (valid) {
+              float* d = P.dbg_reim + g * (2 * P.nbt) + ps * nb + c0;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) { d[j] = __uint_as_float(re[j]); d[P.nbt + j] = __uint_as_float(im[j]); }
+              for (int j = 0; j < 16; ++j) { d[j] = __uint_as_float(re[j]); d[P.nbt + j] = __uint_as_float(im[j]); }
+            }
           }
+          const uint32_t adv_lo = (uint32_t)advw, adv_hi = (uint32_t)(advw >> 32);
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            uint32_t adv = (uint32_t)(advw >> (4 * j)) & 15u;
-            if (adv) {
-              do {
-                if (cur < P.n_mels) prow[cur] = run_lo;
-                run_lo = run_hi; run_hi = 0.f; ++cur;
-              } while (--adv);
-            }
+            const uint32_t adv = ((j < 8 ? adv_lo : adv_hi) >> (4 * (j & 7))) & 15u;
+            if (adv) run = mel_advance(run, adv, prow, P.n_mels);
             const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
             float pw = fmaf(a, a, bq * bq);
-            if (P.power_is_1) pw = sqrtf(pw);
-            run_lo = fmaf(w[j].x, pw, run_lo);
-            run_hi = fmaf(w[j].y, pw, run_hi);
+            if (kPower1) pw = sqrtf(pw);
+            run.lo = fmaf(w[j].x, pw, run.lo);
+            run.hi = fmaf(w[j].y, pw, run.hi);
           }
         }
       }
       // close the running filters and the (empty) ones above them
-      for (; cur < P.n_mels; ++cur) {
-        prow[cur] = run_lo;
-        run_lo = run_hi; run_hi = 0.f;
-      }
+      if (run.cur < P.n_mels) run = mel_advance(run, (uint32_t)(P.n_mels - run.cur), prow, P.n_mels);
       // raw mel sums -> log(max(., clamp)) / norm, one coalesced output row at a time
       __syncwarp();
 #pragma unroll 4
@@ -998,14 +1007,13 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
     P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim;
     const size_t smem = logmel_smem_bytes(p);
-    static thread_local size_t configured = 0;
-    if (configured < smem) {
-      CUDA_TRY(cudaFuncSetAttribute(k_logmel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      configured = smem;
-    }
+    void (*kern)(const LogmelParams) =
+        dbg_reim ? (P.power_is_1 ? k_logmel<true, true> : k_logmel<false, true>)
+                 : (P.power_is_1 ? k_logmel<true, false> : k_logmel<false, false>);
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
     if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
-    k_logmel<<<p->num_sms, kThreads, smem, stream>>>(P);
+    kern<<<p->num_sms, kThreads, smem, stream>>>(P);
     if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
     ++g_launches;
   } else {
