@@ -1,0 +1,27 @@
+"""Where does k_logmel's time go?  Remove pipeline legs one at a time (results invalid, timing only)."""
+import os, sys, ctypes
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+from xtts_b200 import MelPlan, _cabi
+dev = torch.device("cuda:0")
+lib = _cabi.lib()
+plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
+               power=2.0, norm="slaney", device=dev)
+x = torch.rand(64, 220500, device=dev) * 2 - 1
+names = {0: "full", 1: "no A handoff", 2: "no basis loads", 4: "no epilogue", 3: "MMA+epilogue only", 5: "no A, no epi",
+         6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only"}
+for flags in (0, 4, 8, 16, 24, 0):
+    lib.ttts_mel_set_experiment(flags)
+    for _ in range(3):
+        plan.forward(x)
+    torch.cuda.synchronize()
+    lib.ttts_mel_profile_enable(20)
+    for _ in range(20):
+        plan.forward(x)
+    buf = (ctypes.c_float * 20)()
+    n = lib.ttts_mel_profile_collect(buf, 20)
+    ms = sorted(buf[i] for i in range(n))
+    print(f"flags={flags} ({names[flags]:>20s}): k_logmel median {ms[n//2]*1e3:7.1f} us  min {ms[0]*1e3:7.1f} us", flush=True)
+    lib.ttts_mel_profile_enable(0)
+lib.ttts_mel_set_experiment(0)

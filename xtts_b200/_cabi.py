@@ -45,6 +45,7 @@ SYMBOLS = {
     "ttts_mel_status": (ctypes.c_int, [c_void_p, c_void_p]),
     "ttts_mel_stats_accumulate": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p]),
     "ttts_mel_last_launch_count": (c_int32, []),
+    "ttts_mel_set_experiment": (None, [c_int32]),
     "ttts_mel_profile_enable": (ctypes.c_int, [c_int32]),
     "ttts_mel_profile_collect": (ctypes.c_int, [c_void_p, c_int32]),
     "ttts_mel_last_error": (c_char_p, []),

@@ -73,6 +73,7 @@ struct ProfileRing {
   int capacity = 0, count = 0;
 };
 ProfileRing g_prof;
+int g_exp_flags = 0;
 
 int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -103,7 +104,7 @@ struct ttts_mel_plan {
   int nbt = 0;         // passes * nb
   float* d_basis = nullptr;    // [passes][64 k-steps][4 arrays][2 k-halves][nb][4] fp32 (TF32-exact values)
   float2* d_melw = nullptr;    // [nbt] weights of bin i into the running filter pair (cur, cur+1)
-  unsigned long long* d_meladv = nullptr;  // [nbt/16] 4 bits per bin: filters closed before the bin
+  uint32_t* d_meladv = nullptr;  // [nbt/16] bit j: one filter closes before bin 16*i+j
   float* d_norms = nullptr;    // [n_mels] or nullptr
   float* d_cosf = nullptr;     // [512][nbt] plain fp32 folded basis for k_simt
   float* d_sinf = nullptr;
@@ -165,7 +166,7 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
 
   // sparse mel table: every bin feeds at most two ADJACENT filters (triangular filterbanks)
   std::vector<float2> melw(nbt);
-  std::vector<unsigned long long> meladv(nbt / 16, 0ull);
+  std::vector<uint32_t> meladv(nbt / 16, 0u);
   std::vector<float> fbl((size_t)nbt * nm, 0.f);
   int cur = 0;
   for (int i = 0; i < nbt; ++i) {
@@ -179,9 +180,9 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
         if (row[m] != 0.f) { if (first < 0) first = m; last = m; }
       }
       if (first >= 0) {
-        if (last - first > 1 || first < cur || first - cur > 15) {
+        if (last - first > 1 || first < cur || first - cur > 1) {
           delete p;
-          return fail(TTTS_MEL_EINVAL, "filterbank row %d is not two adjacent, non-decreasing filters", kmin + i);
+          return fail(TTTS_MEL_EINVAL, "filterbank row %d: need two adjacent, non-decreasing filters per bin and no filter without bins", kmin + i);
         }
         adv = first - cur;
         cur = first;
@@ -190,7 +191,7 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
       }
     }
     melw[i] = make_float2(wlo, whi);
-    meladv[i >> 4] |= (unsigned long long)adv << (4 * (i & 15));
+    meladv[i >> 4] |= (uint32_t)adv << (i & 15);
   }
 
   // folded, windowed basis.  kappa = n-1 for n = 1..512;  the n = 512 tap appears once, so it
@@ -243,7 +244,7 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   };
   up((void**)&p->d_basis, img.data(), img.size() * 4);
   up((void**)&p->d_melw, melw.data(), melw.size() * sizeof(float2));
-  up((void**)&p->d_meladv, meladv.data(), meladv.size() * sizeof(unsigned long long));
+  up((void**)&p->d_meladv, meladv.data(), meladv.size() * sizeof(uint32_t));
   up((void**)&p->d_cosf, cosf.data(), cosf.size() * 4);
   up((void**)&p->d_sinf, sinf_.data(), sinf_.size() * 4);
   up((void**)&p->d_fb, fbl.data(), fbl.size() * 4);
@@ -349,12 +350,14 @@ __device__ __noinline__ void mbar_timeout(int32_t* status, int code) {
   __threadfence_system();
   __trap();
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int32_t* status, int code) {
-  if (mbar_try_wait(bar, parity)) return;
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, int32_t* status, int code) {
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
   }
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int32_t* status, int code) {
+  if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity, status, code);
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -407,9 +410,6 @@ __device__ __forceinline__ uint32_t elect_one_sync() {
       : "+r"(pred) : "r"(0xffffffffu));
   return pred;
 }
-
-// round-to-nearest TF32 of an fp32 bit pattern
-__device__ __forceinline__ uint32_t tf32_bits(uint32_t u) { return (u + 0x1000u) & 0xFFFFE000u; }
 
 // frame index g (clips concatenated) -> clip b; frame_off is the exclusive prefix of n_frames
 __device__ __forceinline__ int find_clip(const int64_t* __restrict__ frame_off, int B, int64_t g) {
@@ -518,13 +518,14 @@ struct LogmelParams {
   float* out;                 // [B][Tmax][n_mels]
   const float* basis;         // tiled stage images
   const float2* melw;         // [nbt]
-  const unsigned long long* meladv;   // [nbt/16]
+  const uint32_t* meladv;     // [nbt/16]
   const float* norms;         // [n_mels] or null
   int passes, nb, nbt, n_mels;
   float clamp;
   int power_is_1;
   int32_t* status;
   float* dbg_reim;            // optional [total_frames][2*nbt]
+  int exp_flags;              // timing experiments (results invalid): 1 no A handoff, 2 no basis loads, 4 no epilogue
 };
 
 struct __align__(8) LogmelBarriers {
@@ -532,20 +533,6 @@ struct __align__(8) LogmelBarriers {
   uint64_t a_full[kAStages], a_empty[kAStages];
   uint64_t acc_full, acc_empty;
 };
-
-// Running state of the sparse mel contraction: every bin feeds the adjacent filter pair (cur, cur+1).
-struct MelRun { float lo, hi; int cur; };
-
-// Close `adv` filters: park their raw sums in the tile's shared-memory row.  Out of line on purpose: it runs
-// ~n_mels times per frame, while the bin loop that calls it is unrolled 16x and must stay small enough for
-// the instruction cache.
-__device__ __noinline__ MelRun mel_advance(MelRun r, uint32_t adv, float* prow, int n_mels) {
-  do {
-    if (r.cur < n_mels) prow[r.cur] = r.lo;
-    r.lo = r.hi; r.hi = 0.f; ++r.cur;
-  } while (--adv);
-  return r;
-}
 
 template <bool kPower1, bool kDebug>
 __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
@@ -556,8 +543,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   uint8_t* s_b = smem;                                       // basis ring
   uint8_t* s_raw = s_b + (size_t)kBStages * b_stage_bytes;   // raw audio ring
   float2* s_melw = reinterpret_cast<float2*>(s_raw + (size_t)kRawBytes);
-  unsigned long long* s_adv = reinterpret_cast<unsigned long long*>(s_melw + P.nbt);
-  float* s_norm = reinterpret_cast<float*>(s_adv + P.nbt / 16);      // [kMaxMels] mel_norms (or 1)
+  uint32_t* s_adv = reinterpret_cast<uint32_t*>(s_melw + P.nbt);
+  float* s_norm = reinterpret_cast<float*>(s_adv + ((P.nbt / 16 + 3) & ~3));      // [kMaxMels] mel_norms (or 1)
   float* s_park = s_norm + kMaxMels;                                 // [128][n_mels+1] raw mel sums of the tile
   const int park_pitch = P.n_mels + 1;
   LogmelBarriers* bars = reinterpret_cast<LogmelBarriers*>(s_park + ((kTileM * park_pitch + 1) & ~1));
@@ -589,7 +576,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
 
   if (warp == kWarpTma) {
     // ===== basis producer: one bulk copy per k-step stage =====
-    if (lane == 0) {
+    if (lane == 0 && !(P.exp_flags & 2)) {
       uint32_t seq = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
         for (int ps = 0; ps < P.passes; ++ps)
@@ -615,15 +602,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
     uint32_t bseq = 0, cseq = 0, pseq = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        if (!(P.exp_flags & 4)) mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
         for (int c = 0; c < kChunks; ++c, ++cseq) {
 #pragma unroll
           for (int kk = 0; kk < kKC / kKStep; ++kk, ++bseq) {
             // A stage: chunks of parity p use stages 2p (first k-step) and 2p+1 (second k-step)
             const uint32_t as = 2 * (cseq & 1) + kk, ause = cseq >> 1;
             const uint32_t st = bseq % kBStages, use = bseq / kBStages;
-            mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
-            mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+            if (!(P.exp_flags & 1)) mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+            if (!(P.exp_flags & 2)) mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
             tc_fence_after();
             if (elect_one_sync()) {
               const uint32_t a_base = tmem + kColA + as * 32;
@@ -649,7 +636,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           }
         }
       }
-  } else if (warp >= kWarpConv0 && warp < kWarpEpi0) {
+  } else if (warp >= kWarpConv0 && warp < kWarpEpi0 && !(P.exp_flags & 1)) {
     // ===== converters: gather own rows (cp.async) -> fold + TF32 split -> TMEM A operand =====
     // Warp (q, set) owns frame rows 32q..32q+31 of the tile for the chunks c == set (mod 2).  It stages
     // exactly the rows it later reads, so the only synchronisation of the raw-audio ring is
@@ -732,14 +719,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           for (int i = 0; i < 5; ++i) { const float4 v = fw[i]; f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w; }
 #pragma unroll
           for (int i = 0; i < 4; ++i) { const float4 v = mw[i]; m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w; }
+          // TF32 split: hi = x with the 13 low mantissa bits cleared (exactly representable, so it does not matter
+          // how the tensor core would round it), lo = x - hi exactly; the core drops lo's bits below 2^-11 lo.
           uint32_t ehi[16], elo[16], ohi[16], olo[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float e = f[1 + j] + m[15 - j];          // E = f[n] + f[N-n]
             const float o = f[1 + j] - m[15 - j];          // O = f[n] - f[N-n]
-            const uint32_t he = tf32_bits(__float_as_uint(e)), ho = tf32_bits(__float_as_uint(o));
-            ehi[j] = he; elo[j] = tf32_bits(__float_as_uint(e - __uint_as_float(he)));
-            ohi[j] = ho; olo[j] = tf32_bits(__float_as_uint(o - __uint_as_float(ho)));
+            const uint32_t he = __float_as_uint(e) & 0xFFFFE000u, ho = __float_as_uint(o) & 0xFFFFE000u;
+            ehi[j] = he; elo[j] = __float_as_uint(e - __uint_as_float(he));
+            ohi[j] = ho; olo[j] = __float_as_uint(o - __uint_as_float(ho));
           }
           __syncwarp();                                  // every lane has its row in registers: the stage can be refilled
           issue(stage);
@@ -761,7 +750,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           }
         }
     asm volatile("cp.async.wait_all;" ::: "memory");
-  } else if (warp >= kWarpEpi0) {
+  } else if (warp >= kWarpEpi0 && !(P.exp_flags & 4)) {
     // ===== epilogue: power -> sparse mel -> log(clamp) -> / norm =====
     const int q = warp & 3;
     const int r = q * 32 + lane;
@@ -781,54 +770,82 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
       // host table says how many filters close before each bin.  Closed filters are parked as raw sums
       // in shared memory and turned into log-mel in a coalesced pass once the tile is finished, so the
       // accumulator drain below is branch-light and free of transcendental code.
-      MelRun run{0.f, 0.f, 0};
-      float* prow = s_park + r * park_pitch;
-      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
-        tc_fence_after();
-        for (int c0 = 0; c0 < nb; c0 += 16) {
-          uint32_t re[16], im[16];
-          tmem_ld16(tmem + lane_addr + c0, re);
-          tmem_ld16(tmem + lane_addr + kColIm + c0, im);
-          const unsigned long long advw = s_adv[(ps * nb + c0) >> 4];
-          float2 w[16];
-          {
-            const float4* wp = reinterpret_cast<const float4*>(s_melw + ps * nb + c0);
+      float run_lo = 0.f, run_hi = 0.f;            // sums of the filter pair (cur, cur+1)
+      float* pp = s_park + r * park_pitch;         // &park[row][cur]
+      float* const pp_end = pp + P.n_mels;
+      // one 16-bin block: power -> two FMAs per bin; closed filters are parked with a predicated store
+      auto drain16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0) {
+        const uint32_t advw = s_adv[bin0 >> 4];
+        const float4* wp = reinterpret_cast<const float4*>(s_melw + bin0);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { const float4 v = wp[j]; w[2 * j] = make_float2(v.x, v.y); w[2 * j + 1] = make_float2(v.z, v.w); }
-          }
-          tmem_wait_ld();
-          if (c0 + 16 >= nb) {           // accumulators of this pass are in registers: hand TMEM back to the MMA warp
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
-          }
-          if (kDebug) {
-            if (valid) {
-              float* d = P.dbg_reim + g * (2 * P.nbt) + ps * nb + c0;
+        for (int j2 = 0; j2 < 8; ++j2) {
+          const float4 w2 = wp[j2];
 #pragma unroll
-              for (int j = 0; j < 16; ++j) { d[j] = __uint_as_float(re[j]); d[P.nbt + j] = __uint_as_float(im[j]); }
+          for (int h = 0; h < 2; ++h) {
+            const int j = 2 * j2 + h;
+            if (advw & (1u << j)) {                   // warp-uniform: one filter closes before this bin
+              *pp++ = run_lo;
+              run_lo = run_hi; run_hi = 0.f;
             }
-          }
-          const uint32_t adv_lo = (uint32_t)advw, adv_hi = (uint32_t)(advw >> 32);
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const uint32_t adv = ((j < 8 ? adv_lo : adv_hi) >> (4 * (j & 7))) & 15u;
-            if (adv) run = mel_advance(run, adv, prow, P.n_mels);
             const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
             float pw = fmaf(a, a, bq * bq);
             if (kPower1) pw = sqrtf(pw);
-            run.lo = fmaf(w[j].x, pw, run.lo);
-            run.hi = fmaf(w[j].y, pw, run.hi);
+            run_lo = fmaf(h ? w2.z : w2.x, pw, run_lo);
+            run_hi = fmaf(h ? w2.w : w2.y, pw, run_hi);
+          }
+        }
+      };
+      auto dump16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0) {
+        if (kDebug) {
+          if (valid) {
+            float* d = P.dbg_reim + g * (2 * P.nbt) + bin0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { d[j] = __uint_as_float(re[j]); d[P.nbt + j] = __uint_as_float(im[j]); }
+          }
+        }
+      };
+      auto release_acc = [&]() {        // accumulators of this pass are in registers: hand TMEM back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
+      };
+      const int nblk = nb >> 4;
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
+        tc_fence_after();
+        // two register sets: the TMEM load of block i+1 is in flight while block i is reduced
+        uint32_t reA[16], imA[16], reB[16], imB[16];
+        tmem_ld16(tmem + lane_addr, reA);
+        tmem_ld16(tmem + lane_addr + kColIm, imA);
+        for (int blk = 0; blk < nblk; blk += 2) {
+          tmem_wait_ld();                                          // set A = block blk
+          if (blk + 1 < nblk) {
+            tmem_ld16(tmem + lane_addr + (blk + 1) * 16, reB);
+            tmem_ld16(tmem + lane_addr + kColIm + (blk + 1) * 16, imB);
+          } else {
+            release_acc();
+          }
+          dump16(reA, imA, ps * nb + blk * 16);
+          if (!(P.exp_flags & 8)) drain16(reA, imA, ps * nb + blk * 16);
+          if (blk + 1 < nblk) {
+            tmem_wait_ld();                                        // set B = block blk+1
+            if (blk + 2 < nblk) {
+              tmem_ld16(tmem + lane_addr + (blk + 2) * 16, reA);
+              tmem_ld16(tmem + lane_addr + kColIm + (blk + 2) * 16, imA);
+            } else {
+              release_acc();
+            }
+            dump16(reB, imB, ps * nb + (blk + 1) * 16);
+            if (!(P.exp_flags & 8)) drain16(reB, imB, ps * nb + (blk + 1) * 16);
           }
         }
       }
       // close the running filters and the (empty) ones above them
-      if (run.cur < P.n_mels) run = mel_advance(run, (uint32_t)(P.n_mels - run.cur), prow, P.n_mels);
+      for (; pp < pp_end; ++pp) { *pp = run_lo; run_lo = run_hi; run_hi = 0.f; }
       // raw mel sums -> log(max(., clamp)) / norm, one coalesced output row at a time
       __syncwarp();
 #pragma unroll 4
-      for (int rr = 0; rr < 32; ++rr) {
+      for (int rr = 0; rr < ((P.exp_flags & 16) ? 0 : 32); ++rr) {
         const unsigned long long pr = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr);
         const int ok = __shfl_sync(0xffffffffu, (int)valid, rr);
         if (!ok) continue;
@@ -965,7 +982,7 @@ __global__ void __launch_bounds__(kMaxMels* kStatRows) k_stats(const float* __re
 namespace {
 
 size_t logmel_smem_bytes(const ttts_mel_plan* p) {
-  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawBytes + (size_t)p->nbt * sizeof(float2) + (size_t)p->nbt / 2 +
+  size_t s = (size_t)kBStages * p->nb * 128 + (size_t)kRawBytes + (size_t)p->nbt * sizeof(float2) + (size_t)(p->nbt / 16 + 4) * 4 +
              kMaxMels * 4 + (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + sizeof(LogmelBarriers) + 16;
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
 }
@@ -1005,7 +1022,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.xp = w.xp; P.Lp = w.Lp; P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
     P.out = out; P.basis = p->d_basis; P.melw = p->d_melw; P.meladv = p->d_meladv; P.norms = p->d_norms;
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
-    P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim;
+    P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim; P.exp_flags = g_exp_flags;
     const size_t smem = logmel_smem_bytes(p);
     void (*kern)(const LogmelParams) =
         dbg_reim ? (P.power_is_1 ? k_logmel<true, true> : k_logmel<false, true>)
@@ -1111,3 +1128,5 @@ extern "C" int ttts_mel_profile_collect(float* ms_out, int32_t capacity) {
   g_prof.count = 0;
   return n;
 }
+
+extern "C" void ttts_mel_set_experiment(int32_t flags) { g_exp_flags = flags; }
