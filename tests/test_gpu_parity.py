@@ -193,3 +193,60 @@ def test_mel_stats(dev):
     got = acc.cpu().numpy() / 2
     assert got[160] == ref[160] == sum(orc.frame_count(L) for L in lens)
     assert np.allclose(got[:160], ref[:160], rtol=1e-12, atol=1e-9)
+
+
+def test_config3_ragged_sweep_buckets_masks_stats(dev):
+    """BASELINE config 3: 256 clips of 1..30 s, length-bucketed, padding masks, mel_norms statistics."""
+    from xtts_b200 import MelPlan
+    from xtts_b200.sweep import MelSweep, norms_from_stats
+    plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0,
+                   f_max=8000, power=2.0, norm="slaney", device=dev)
+    rng = np.random.default_rng(1234)
+    lens = [int(round(22050 * u)) for u in rng.uniform(1.0, 30.0, size=256)]
+    sweep = MelSweep(plan, lens, bucket_seconds=2.0, max_clips=64)
+    assert len({b.max_len // 44100 for b in sweep.buckets}) <= 15
+    clips = {}
+
+    def fetch(idx, max_len):
+        wav = torch.zeros(len(idx), max_len, device=dev)
+        for k, i in enumerate(idx):
+            g = torch.Generator(device=dev).manual_seed(5000 + i)
+            clips[i] = torch.rand(lens[i], device=dev, generator=g) * 2 - 1
+            wav[k, :lens[i]] = clips[i]
+            wav[k, lens[i]:] = 0.777                      # junk in the padding must not leak into the clip
+        return wav, torch.tensor([lens[i] for i in idx])
+
+    got = {}
+
+    def sink(idx, mel, n_frames):
+        nf = n_frames.cpu().tolist()
+        T = mel.shape[2]
+        mask = torch.arange(T, device=dev)[None, :] >= n_frames[:, None]
+        assert bool((mel.transpose(1, 2)[mask] == 0).all())              # padded frames are exactly 0.0
+        for k, i in enumerate(idx):
+            assert nf[k] == orc.frame_count(lens[i])                     # bit-exact frame counts
+            got[i] = mel[k, :, :nf[k]].clone()
+
+    acc = sweep.run_stats(fetch, sink=sink)
+    plan.status()
+    assert sorted(got) == list(range(256))
+    # values: a 16-clip sample against the reference call sequence, one clip per call (mel_extract.py:15-27)
+    for i in range(0, 256, 16):
+        ref = orc.callsite_logmel(clips[i].cpu().numpy()[None, :], orc.V1, None).numpy()[0]
+        assert ref.shape == tuple(got[i].shape)
+        assert np.abs(_np(got[i]) - ref).max() <= TOL, i
+    # statistics: fp64 reduction of the produced log-mel
+    ref_acc = np.zeros(161)
+    for i in range(256):
+        lm = _np(got[i]).astype(np.float64)
+        ref_acc[:80] += lm.sum(1); ref_acc[80:160] += (lm * lm).sum(1); ref_acc[160] += lm.shape[1]
+    a = acc.cpu().numpy()
+    assert a[160] == ref_acc[160] == sum(orc.frame_count(L) for L in lens)
+    assert np.allclose(a[:160], ref_acc[:160], rtol=1e-11)
+    mean, std = norms_from_stats(acc)
+    assert np.allclose(mean.cpu().numpy(), ref_acc[:80] / ref_acc[160], rtol=1e-6)
+    # second pass with the derived norms applied == first pass / norms
+    plan.set_norms(mean)
+    wav, l = fetch([3, 77], max(lens[3], lens[77]))
+    y, nf, _ = plan.forward(wav, l.to(dev), t_max=plan.frames(max(lens[3], lens[77])))
+    assert np.abs(_np(y[0, :int(nf[0])].T) - _np(got[3]) / mean.cpu().numpy()[:, None]).max() <= 1e-5

@@ -1,0 +1,133 @@
+"""Dataset-scale preprocessing on top of the front-end: length buckets, rank sharding, mel_norms.
+
+Restates the shape of the reference's preprocessing drivers -- ``ttts/prepare/save_mel_to_disk.py:16-29``
+and ``ttts/prepare/mel_extract.py:8-27`` (one clip per call, all workers on cuda:0, skip-if-exists
+resume) -- as a batched, sharded sweep: utterances are grouped into length buckets, buckets are
+dealt to ranks so that every rank gets the same number of frames (longest-processing-time first),
+and the only collective is one fp64 all-reduce of the mel_norms sufficient statistics
+``[sum_m | sumsq_m | count]`` (2*n_mels+1 doubles), the pattern of the EMA codebook statistics in
+``ttts/vqvae/xtts_dvae.py:104-110``.  No data-path collective: clips never span GPUs.
+
+Everything here is host logic (pure Python / torch.distributed) and runs on CPU with the ``gloo``
+backend in the tests; the per-batch compute is ``MelPlan.forward`` + ``MelPlan.stats_accumulate``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, Iterable, List, Optional, Sequence, Tuple
+
+import torch
+
+
+@dataclass(frozen=True)
+class Bucket:
+    """Indices of the utterances of one length bucket, padded to ``max_len`` samples."""
+    indices: Tuple[int, ...]
+    max_len: int
+    frames: int          # sum of frame counts of the member clips
+
+
+def frame_count(length: int, n_fft: int = 1024, hop: int = 256, pad: int = 512) -> int:
+    return 1 + (length + 2 * pad - n_fft) // hop
+
+
+def make_buckets(lengths: Sequence[int], bucket_width: int, max_clips: int = 64, *, n_fft: int = 1024,
+                 hop: int = 256, pad: int = 512, max_batch_samples: int = 64 * 220500) -> List[Bucket]:
+    """Group clips whose lengths fall in the same ``bucket_width``-sample band; split a band into batches of
+    at most ``max_clips`` clips / ``max_batch_samples`` padded samples.  Deterministic (stable sort)."""
+    order = sorted(range(len(lengths)), key=lambda i: (int(lengths[i]) // bucket_width, int(lengths[i]), i))
+    out: List[Bucket] = []
+    cur: List[int] = []
+    cur_band = None
+    cur_max = 0
+
+    def flush():
+        nonlocal cur, cur_max
+        if cur:
+            out.append(Bucket(tuple(cur), cur_max,
+                              sum(frame_count(int(lengths[i]), n_fft, hop, pad) for i in cur)))
+        cur, cur_max = [], 0
+
+    for i in order:
+        L = int(lengths[i])
+        band = L // bucket_width
+        new_max = max(cur_max, L)
+        if cur and (band != cur_band or len(cur) >= max_clips or new_max * (len(cur) + 1) > max_batch_samples):
+            flush()
+            new_max = L
+        cur_band = band
+        cur.append(i)
+        cur_max = new_max
+    flush()
+    return out
+
+
+def shard_buckets(buckets: Sequence[Bucket], world_size: int) -> List[List[int]]:
+    """Longest-processing-time-first assignment of buckets (by frame count) to ranks.
+    Returns, per rank, the bucket indices it owns.  Every bucket is owned by exactly one rank."""
+    loads = [0] * world_size
+    owned: List[List[int]] = [[] for _ in range(world_size)]
+    for j in sorted(range(len(buckets)), key=lambda j: (-buckets[j].frames, j)):
+        r = min(range(world_size), key=lambda r: (loads[r], r))
+        owned[r].append(j)
+        loads[r] += buckets[j].frames
+    for r in range(world_size):
+        owned[r].sort()
+    return owned
+
+
+def allreduce_stats(acc: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum the fp64 statistics vector over ranks (NCCL over NVLink on GPUs, gloo on CPU)."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+    return acc
+
+
+def norms_from_stats(acc: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """mel_norms[m] = mean of log-mel[m] over all valid frames (tortoise convention);
+    also returns the per-channel standard deviation."""
+    n = (acc.numel() - 1) // 2
+    cnt = acc[2 * n]
+    mean = acc[:n] / cnt
+    var = (acc[n:2 * n] / cnt - mean * mean).clamp_min(0)
+    return mean.to(torch.float32), var.sqrt().to(torch.float32)
+
+
+class MelSweep:
+    """Two-pass sweep of a corpus: pass 1 accumulates statistics, all-reduces them and derives mel_norms;
+    pass 2 (or any later ``TorchMelSpectrogram`` call) applies them.
+
+    ``fetch(indices, max_len) -> (wav[B, max_len] float32 CUDA tensor, lengths[B] int64)`` supplies a batch;
+    ``sink(indices, mel[B, n_mels, T], n_frames[B])`` consumes results (the reference's per-file
+    ``torch.save(mel, f'{wav}.mel.pth')``, mel_extract.py:27); ``done(index) -> bool`` is the reference's
+    skip-if-exists resume rule (mel_extract.py:10-12)."""
+
+    def __init__(self, plan, lengths: Sequence[int], *, bucket_seconds: float = 2.0, sample_rate: int = 22050,
+                 max_clips: int = 64, rank: int = 0, world_size: int = 1):
+        self.plan = plan
+        self.lengths = [int(v) for v in lengths]
+        self.buckets = make_buckets(self.lengths, int(bucket_seconds * sample_rate), max_clips,
+                                    n_fft=plan.n_fft, hop=plan.hop, pad=plan.pad)
+        self.owned = shard_buckets(self.buckets, world_size)
+        self.rank, self.world_size = rank, world_size
+
+    def my_buckets(self) -> List[Bucket]:
+        return [self.buckets[j] for j in self.owned[self.rank]]
+
+    def run_stats(self, fetch: Callable, done: Optional[Callable[[int], bool]] = None,
+                  sink: Optional[Callable] = None) -> torch.Tensor:
+        """Pass 1 on this rank's buckets; returns the all-reduced statistics (identical on every rank)."""
+        acc = torch.zeros(2 * self.plan.n_mels + 1, dtype=torch.float64, device=self.plan.device)
+        self.plan.set_norms(None)
+        for b in self.my_buckets():
+            idx = [i for i in b.indices if not (done and done(i))]
+            if not idx:
+                continue
+            wav, lens = fetch(idx, b.max_len)
+            t_max = self.plan.frames(int(max(self.lengths[i] for i in idx)))
+            mel, n_frames, _ = self.plan.forward(wav, lens, t_max=t_max)
+            self.plan.stats_accumulate(mel, n_frames, acc)
+            if sink is not None:
+                sink(idx, mel.transpose(1, 2), n_frames)
+        return allreduce_stats(acc)
