@@ -117,6 +117,7 @@ def run_reference(args):
     if rank != 0:
         return
     import torch
+    torch.set_num_threads(os.cpu_count() or 1)      # torchrun pins OMP_NUM_THREADS=1: use every host core instead
     x = torch.rand(B_CLIPS, CLIP_LEN, generator=torch.Generator().manual_seed(1234)) * 2 - 1
     val, sec_per_step, cores = cpu_reference_throughput(args.steps, args.warmup, x)
     line = {
@@ -273,6 +274,7 @@ def run_ours(args):
         cpu_line = None
         if world == 1 and not args.no_cpu_baseline:
             xs = inputs[0].cpu()
+            torch.set_num_threads(os.cpu_count() or 1)
             val, sec, cores = cpu_reference_throughput(12, 1, xs)
             cpu_line = {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port",
                         "sample": "12 passes of the same 64x10 s batch through the reference's call sequence "
