@@ -293,7 +293,7 @@ def run_ours(args):
                     "how": "TorchMelSpectrogram.forward on pinned host batches, double-buffered H2D/D2H streams, wall clock",
                     "max_abs_diff_vs_resident": chk},
             "gpu_launches": launches,
-            "kernels_per_step": {"k_prep": 1, "k_pad": 1, "k_logmel": 1},
+            "kernels_per_step": {"k_prep(+edge buffers)": 1, "k_logmel": 1},
             "roofline": {"bound": "tensor", "kernel": "k_logmel", "achieved": achieved, "peak": tf32_peak,
                          "unit": "TFLOP/s", "frac": (achieved / tf32_peak) if achieved else None, "traffic": traffic,
                          "kernel_ms": k_ms, "kernel_share_of_step": (k_ms / (ms_total / K)) if k_ms else None,

@@ -250,3 +250,30 @@ def test_config3_ragged_sweep_buckets_masks_stats(dev):
     wav, l = fetch([3, 77], max(lens[3], lens[77]))
     y, nf, _ = plan.forward(wav, l.to(dev), t_max=plan.frames(max(lens[3], lens[77])))
     assert np.abs(_np(y[0, :int(nf[0])].T) - _np(got[3]) / mean.cpu().numpy()[:, None]).max() <= 1e-5
+
+
+def test_unaligned_rows_take_the_padded_workspace_path(dev, v1):
+    """Row stride not a multiple of 4 floats (or a misaligned base): same results through k_pad + xp."""
+    x = orc.synth("uniform", 3, 9001, 31)
+    big = torch.zeros(3, 9003, device=dev)
+    view = big[:, 1:9002]                       # stride 9003, base offset 4 B: not 16 B addressable
+    view.copy_(torch.from_numpy(x))
+    assert view.stride(0) == 9003 and view.data_ptr() % 16 != 0
+    plan = v1._plan_for(dev)
+    a, nf, _ = plan.forward(view)
+    b, _, _ = plan.forward(torch.from_numpy(x).to(dev))
+    plan.status()
+    ref = orc.callsite_logmel(x, orc.V1, orc.default_mel_norms(80)).numpy()
+    assert np.abs(_np(a.transpose(1, 2)) - ref).max() <= TOL
+    assert np.abs(_np(b.transpose(1, 2)) - ref).max() <= TOL
+    assert float((a - b).abs().max()) <= 2e-5
+
+
+def test_short_and_edge_heavy_clips(dev, v1):
+    """Clips of <= 8 frames live entirely in the edge buffer; 9..12 frames mix both sources."""
+    for L in (513, 1800, 2047, 2048, 2049, 2303, 2304, 2305, 2560, 2816, 3000, 3072, 3328):
+        x = orc.synth("uniform", 5, L, 700 + L)
+        y = v1(torch.from_numpy(x).to(dev))
+        ref = orc.callsite_logmel(x, orc.V1, orc.default_mel_norms(80)).numpy()
+        assert tuple(y.shape) == ref.shape, L
+        assert np.abs(_np(y) - ref).max() <= TOL, L

@@ -50,8 +50,12 @@ constexpr int kConvDepth = 2;           // raw-audio stages per converter warp (
 constexpr int kRawPitch = 20;          // floats per staged row (80 B: conflict-free row-per-thread LDS.128)
 constexpr int kConvStageBytes = 2 * 32 * kRawPitch * 4;      // 32 rows x (forward window + mirrored window)
 constexpr int kRawBytes = kConvWarps * kConvDepth * kConvStageBytes;
+constexpr int kEdgeA = 2880;            // per-clip edge buffer, region A: padded samples of frames 0..7
+constexpr int kEdgeB = 1792;            //                       region B: padded samples of the last 4 frames
+constexpr int kEdgeClip = kEdgeA + kEdgeB;
 constexpr int kTmemCols = 512;
-constexpr int kColIm = kNBMax;         // accumulator columns: re [0,NB), im [192,192+NB)
+constexpr int kAccStride = kNBMax;     // accumulator buffers: one (re [0,nb) | im [192,192+nb)) when nb > 96,
+                                       // two (buffer b at 192 b: re [0,nb) | im [96,96+nb)) when nb <= 96
 constexpr int kColA = 2 * kNBMax;      // A ring: 4 stages x 32 columns (E_hi,E_lo,O_hi,O_lo x 8 = one k-step)
 constexpr int kAStages = 4;
 constexpr int kThreads = 512;
@@ -159,7 +163,12 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   p->cfg = *cfg;
   p->kmin = kmin;
   p->n_live = kmax - kmin + 1;
-  p->passes = (p->n_live + kNBMax - 1) / kNBMax;
+  int nb_cap = kNBMax;
+  if (const char* e = getenv("TTTS_MEL_NB_MAX")) {          // tuning knob: 96 selects double-buffered accumulators
+    const int v = atoi(e);
+    if (v >= 16 && v <= kNBMax && v % 16 == 0) nb_cap = v;
+  }
+  p->passes = (p->n_live + nb_cap - 1) / nb_cap;
   p->nb = (int)align_up((size_t)((p->n_live + p->passes - 1) / p->passes), 16);
   p->nbt = p->passes * p->nb;
   const int nb = p->nb, nbt = p->nbt;
@@ -299,7 +308,8 @@ struct Workspace {
   int32_t* status;      // [64] word 0 = device error code
   int64_t* frame_off;   // [B+1]
   int32_t* n_frames;    // [B]
-  float* xp;            // [B][Lp]
+  float* xp;            // [B][Lp]   (k_simt and unaligned inputs only)
+  float* edge;          // [B][kEdgeClip] reflect-padded samples of each clip's first and last frames
   int64_t Lp;
   size_t bytes;
 };
@@ -313,6 +323,7 @@ Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
   w.status = (int32_t*)(b + off); off += 256;
   w.frame_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.n_frames = (int32_t*)(b + off); off += align_up((size_t)B * 4, 256);
+  w.edge = (float*)(b + off); off += align_up((size_t)B * kEdgeClip * 4, 256);
   w.xp = (float*)(b + off); off += align_up((size_t)B * (size_t)w.Lp * 4, 256);
   w.bytes = off;
   return w;
@@ -426,21 +437,36 @@ __device__ __forceinline__ int find_clip(const int64_t* __restrict__ frame_off, 
 // ------------------------------------------------------------------------------------------
 // k_prep: lengths -> n_frames, frame_off (exclusive prefix), status
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) k_prep(const int64_t* __restrict__ lengths, int B, int64_t Lmax, int pad,
+__device__ __forceinline__ long long clip_frames(long long L, long long Lmax, int pad, int Tmax, int* err) {
+  long long T = 0;
+  if (L > pad && L <= Lmax && L + 2 * pad >= kNfft) T = 1 + (L + 2 * pad - kNfft) / kHop;
+  else *err = 1;                                // bad length
+  if (T > Tmax) { T = Tmax; *err = 2; }
+  return T;
+}
+
+__device__ void edge_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
+                          int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, int b);
+
+// Block 0: frame counts + prefix.  Blocks 1..B (only when `edge` is given): the edge buffer of clip blockIdx.x-1.
+__global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, int64_t row_stride, float* __restrict__ edge,
+                                               const int64_t* __restrict__ lengths, int B, int64_t Lmax, int pad,
                                                int Tmax, int32_t* __restrict__ n_frames,
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
                                                int32_t* __restrict__ status) {
+  if (blockIdx.x > 0) { edge_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, blockIdx.x - 1); return; }
   __shared__ long long part[1024];
   const int tid = threadIdx.x;
+  if (tid == 0) *status = 0;
+  __syncthreads();
   const int per = (B + 1023) / 1024;
   const int b0 = tid * per, b1 = min(B, b0 + per);
   long long sum = 0;
   for (int b = b0; b < b1; ++b) {
     const long long L = lengths ? lengths[b] : Lmax;
-    long long T = 0;
-    if (L > pad && L <= Lmax && L + 2 * pad >= kNfft) T = 1 + (L + 2 * pad - kNfft) / kHop;
-    else atomicExch(status, 1);                 // bad length
-    if (T > Tmax) { T = Tmax; atomicExch(status, 2); }
+    int err = 0;
+    const long long T = clip_frames(L, Lmax, pad, Tmax, &err);
+    if (err) atomicExch(status, err);
     n_frames[b] = (int32_t)T;
     if (n_frames_user) n_frames_user[b] = (int32_t)T;
     sum += T;
@@ -495,6 +521,33 @@ __global__ void __launch_bounds__(256) k_pad(const float* __restrict__ wav, int6
 }
 
 // ------------------------------------------------------------------------------------------
+// edge buffers (k_prep blocks 1..B): only the frames that touch the reflect padding are materialised (first frames and last
+// <= 3 frames of every clip, or the whole clip when it has <= 8 frames); every other frame is read
+// straight from the caller's waveform by k_logmel.  edge[b] = A: padded[0, 2880) | B: padded[256 (T-4), +1792)
+// ------------------------------------------------------------------------------------------
+__device__ void edge_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
+                          int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, int b) {
+  const int64_t L = lengths ? lengths[b] : Lmax;
+  int err = 0;
+  const int T = (int)clip_frames(L, Lmax, pad, Tmax, &err);
+  const float* __restrict__ src = wav + (int64_t)b * row_stride;
+  float* __restrict__ dst = edge + (int64_t)b * kEdgeClip;
+  const bool okL = T > 0 && err != 1;
+  const int64_t startB = (int64_t)kHop * (T - 4);
+  for (int i = threadIdx.x; i < kEdgeClip; i += blockDim.x) {
+    const bool inB = i >= kEdgeA;
+    int64_t s = (inB ? startB + (i - kEdgeA) : (int64_t)i) - pad;
+    float v = 0.f;
+    if (okL && (!inB || T > 8) && s >= -(int64_t)pad && s < L + pad) {
+      if (s < 0) s = -s;
+      if (s >= L) s = 2 * (L - 1) - s;
+      v = __ldg(src + s);
+    }
+    dst[i] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // k_mask: make_pad_mask (ttts/utils/utils.py:77-103): mask[b][t] = t >= n_frames[b]
 // ------------------------------------------------------------------------------------------
 __global__ void k_mask(const int32_t* __restrict__ n_frames, int B, int Tmax, uint8_t* __restrict__ mask) {
@@ -509,8 +562,12 @@ __global__ void k_mask(const int32_t* __restrict__ n_frames, int B, int Tmax, ui
 // k_logmel: the fused tcgen05 kernel
 // ------------------------------------------------------------------------------------------
 struct LogmelParams {
-  const float* xp;            // [B][Lp] reflect-padded clips
-  int64_t Lp;
+  const float* src;           // direct: the caller's waveform [B][src_stride]; else workspace xp [B][Lp]
+  int64_t src_stride;
+  const float* edge;          // [B][kEdgeClip] (direct mode)
+  const int64_t* lengths;     // [B] or null
+  int64_t Lmax;
+  int direct, pad;
   const int64_t* frame_off;   // [B+1]
   const int32_t* n_frames;    // [B]
   int B;
@@ -531,7 +588,7 @@ struct LogmelParams {
 struct __align__(8) LogmelBarriers {
   uint64_t b_full[kBStages], b_empty[kBStages];
   uint64_t a_full[kAStages], a_empty[kAStages];
-  uint64_t acc_full, acc_empty;
+  uint64_t acc_full[2], acc_empty[2];
 };
 
 template <bool kPower1, bool kDebug>
@@ -561,8 +618,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStages; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
     for (int i = 0; i < kAStages; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
-    mbar_init(smem_u32(&bars->acc_full), 1);
-    mbar_init(smem_u32(&bars->acc_empty), 4);
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->acc_full[i]), 1); mbar_init(smem_u32(&bars->acc_empty[i]), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpTmem) {
@@ -573,6 +629,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
+  const uint32_t acc_bufs = nb <= 96 ? 2u : 1u;              // double-buffered accumulators when they fit
+  const uint32_t col_im = nb <= 96 ? 96u : (uint32_t)kNBMax;
 
   if (warp == kWarpTma) {
     // ===== basis producer: one bulk copy per k-step stage =====
@@ -598,11 +656,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
     const uint32_t desc_lo0 = (((uint32_t)nb * 16u) >> 4) << 16;
     const uint32_t arr16 = ((uint32_t)nb * 32u) >> 4;           // one operand array, in 16 B units
     const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
-    const uint32_t d_re = tmem, d_im = tmem + kColIm;
     uint32_t bseq = 0, cseq = 0, pseq = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        if (!(P.exp_flags & 4)) mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        const uint32_t abuf = pseq % acc_bufs, ause_acc = pseq / acc_bufs;
+        const uint32_t d_re = tmem + abuf * kAccStride, d_im = d_re + col_im;
+        if (!(P.exp_flags & 4)) mbar_wait(smem_u32(&bars->acc_empty[abuf]), (ause_acc & 1) ^ 1, P.status, 201);
         for (int c = 0; c < kChunks; ++c, ++cseq) {
 #pragma unroll
           for (int kk = 0; kk < kKC / kKStep; ++kk, ++bseq) {
@@ -630,7 +689,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
               tc_commit(smem_u32(&bars->b_empty[st]));       // basis stage free once these MMAs retire
               tc_commit(smem_u32(&bars->a_empty[as]));       // A stage free
               if (c == kChunks - 1 && kk == kKC / kKStep - 1)
-                tc_commit(smem_u32(&bars->acc_full));        // accumulators of this pass complete
+                tc_commit(smem_u32(&bars->acc_full[abuf]));  // accumulators of this pass complete
             }
             __syncwarp();
           }
@@ -652,25 +711,34 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
     // issue cursor (runs kConvDepth chunks ahead of the consume cursor)
     int i_tile = blockIdx.x, i_ps = 0, i_c = set;
     int32_t off_f[8], off_m[4];
+    uint32_t rows_valid = 0, rows_edge = 0;            // per row of this warp: has a frame / lives in the edge buffer
     auto load_row_offsets = [&](int tile) {
-      int32_t base = -1;
+      int32_t base = 0;
+      bool valid = false, edge = false;
       if (tile < num_tiles) {
         const int64_t g = (int64_t)tile * kTileM + q * 32 + lane;
         if (g < total_frames) {
+          valid = true;
           const int b = find_clip(P.frame_off, P.B, g);
-          base = (int32_t)((int64_t)b * P.Lp + (g - P.frame_off[b]) * kHop);
+          const int t = (int)(g - P.frame_off[b]);
+          if (!P.direct) {
+            base = (int32_t)((int64_t)b * P.src_stride + (int64_t)t * kHop);
+          } else {
+            const int T = P.n_frames[b];
+            const int64_t L = P.lengths ? P.lengths[b] : P.Lmax;
+            const int64_t s0 = (int64_t)t * kHop - P.pad;
+            if (T <= 8 || s0 < 0) { edge = true; base = b * kEdgeClip + t * kHop; }
+            else if (s0 + kNfft > L) { edge = true; base = b * kEdgeClip + kEdgeA + (t - (T - 4)) * kHop; }
+            else base = (int32_t)((int64_t)b * P.src_stride + s0);
+          }
         }
       }
+      rows_valid = __ballot_sync(0xffffffffu, valid);
+      rows_edge = __ballot_sync(0xffffffffu, edge);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int32_t v = __shfl_sync(0xffffffffu, base, fr + 4 * k);
-        off_f[k] = v >= 0 ? v + 4 * fj : -1;
-      }
+      for (int k = 0; k < 8; ++k) off_f[k] = __shfl_sync(0xffffffffu, base, fr + 4 * k) + 4 * fj;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int32_t v = __shfl_sync(0xffffffffu, base, mr + 8 * k);
-        off_m[k] = v >= 0 ? v + (kNfft - kKC) + 4 * mj : -1;
-      }
+      for (int k = 0; k < 4; ++k) off_m[k] = __shfl_sync(0xffffffffu, base, mr + 8 * k) + (kNfft - kKC) + 4 * mj;
     };
     auto issue = [&](uint32_t stage) {
       if (i_tile < num_tiles) {
@@ -681,15 +749,19 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         if (fj < 5) {
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
-            const bool ok = off_f[k] >= 0;
-            cp_async16(fw + (uint32_t)((fr + 4 * k) * kRawPitch + 4 * fj) * 4u, P.xp + (ok ? off_f[k] + adv : 0), ok ? 16u : 0u);
+            const int row = fr + 4 * k;
+            const bool ok = (rows_valid >> row) & 1u;
+            const float* bp = ((rows_edge >> row) & 1u) ? P.edge : P.src;
+            cp_async16(fw + (uint32_t)(row * kRawPitch + 4 * fj) * 4u, ok ? bp + (off_f[k] + adv) : P.src, ok ? 16u : 0u);
           }
         }
         // mirrored window: xp[row + 1008 - 16c + i], i = 0..15 (tap N-n is i = 15-j)
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const bool ok = off_m[k] >= 0;
-          cp_async16(mw + (uint32_t)((mr + 8 * k) * kRawPitch + 4 * mj) * 4u, P.xp + (ok ? off_m[k] - adv : 0), ok ? 16u : 0u);
+          const int row = mr + 8 * k;
+          const bool ok = (rows_valid >> row) & 1u;
+          const float* bp = ((rows_edge >> row) & 1u) ? P.edge : P.src;
+          cp_async16(mw + (uint32_t)(row * kRawPitch + 4 * mj) * 4u, ok ? bp + (off_m[k] - adv) : P.src, ok ? 16u : 0u);
         }
         // advance the cursor over (tile, pass, chunk of my parity)
         i_c += 2;
@@ -804,24 +876,27 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           }
         }
       };
+      uint32_t abuf = 0;
       auto release_acc = [&]() {        // accumulators of this pass are in registers: hand TMEM back to the MMA warp
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
+        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty[abuf]));
       };
       const int nblk = nb >> 4;
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
+        abuf = pseq % acc_bufs;
+        mbar_wait(smem_u32(&bars->acc_full[abuf]), (pseq / acc_bufs) & 1, P.status, 501);
         tc_fence_after();
+        const uint32_t t_re = tmem + lane_addr + abuf * kAccStride, t_im = t_re + col_im;
         // two register sets: the TMEM load of block i+1 is in flight while block i is reduced
         uint32_t reA[16], imA[16], reB[16], imB[16];
-        tmem_ld16(tmem + lane_addr, reA);
-        tmem_ld16(tmem + lane_addr + kColIm, imA);
+        tmem_ld16(t_re, reA);
+        tmem_ld16(t_im, imA);
         for (int blk = 0; blk < nblk; blk += 2) {
           tmem_wait_ld();                                          // set A = block blk
           if (blk + 1 < nblk) {
-            tmem_ld16(tmem + lane_addr + (blk + 1) * 16, reB);
-            tmem_ld16(tmem + lane_addr + kColIm + (blk + 1) * 16, imB);
+            tmem_ld16(t_re + (blk + 1) * 16, reB);
+            tmem_ld16(t_im + (blk + 1) * 16, imB);
           } else {
             release_acc();
           }
@@ -830,8 +905,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
           if (blk + 1 < nblk) {
             tmem_wait_ld();                                        // set B = block blk+1
             if (blk + 2 < nblk) {
-              tmem_ld16(tmem + lane_addr + (blk + 2) * 16, reA);
-              tmem_ld16(tmem + lane_addr + kColIm + (blk + 2) * 16, imA);
+              tmem_ld16(t_re + (blk + 2) * 16, reA);
+              tmem_ld16(t_im + (blk + 2) * 16, imA);
             } else {
               release_acc();
             }
@@ -1002,11 +1077,15 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   if ((int64_t)B * w.Lp >= (int64_t)1 << 31) return fail(TTTS_MEL_EINVAL, "batch too large for 32-bit row offsets: split it");
   cudaStream_t stream = (cudaStream_t)stream_;
 
-  CUDA_TRY(cudaMemsetAsync(w.status, 0, 256, stream));
-  k_prep<<<1, 1024, 0, stream>>>(lengths, B, Lmax, p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.status);
-  ++g_launches;
   const int vec_ok = (row_stride % 4 == 0) && (((uintptr_t)wav & 15) == 0);
-  {
+  // k_logmel reads the caller's waveform directly when it is 16 B-addressable; only the frames that touch
+  // the reflect padding go through a small edge buffer.  Otherwise (and for k_simt) the clips are padded
+  // into the workspace first.
+  const bool direct = impl == Impl::Tcgen05 && vec_ok && (int64_t)B * row_stride < ((int64_t)1 << 31);
+  k_prep<<<direct ? B + 1 : 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, lengths, B, Lmax,
+                                                  p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.status);
+  ++g_launches;
+  if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
     dim3 grid((unsigned)((vecs + 255) / 256 > 4096 ? 4096 : (vecs + 255) / 256), (unsigned)B);
     k_pad<<<grid, 256, 0, stream>>>(wav, row_stride, lengths, Lmax, p->cfg.pad, w.xp, w.Lp, vec_ok);
@@ -1019,7 +1098,9 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   }
   if (impl == Impl::Tcgen05) {
     LogmelParams P{};
-    P.xp = w.xp; P.Lp = w.Lp; P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
+    P.src = direct ? wav : w.xp; P.src_stride = direct ? row_stride : w.Lp; P.edge = w.edge;
+    P.lengths = lengths; P.Lmax = Lmax; P.direct = direct; P.pad = p->cfg.pad;
+    P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
     P.out = out; P.basis = p->d_basis; P.melw = p->d_melw; P.meladv = p->d_meladv; P.norms = p->d_norms;
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
     P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim; P.exp_flags = g_exp_flags;
