@@ -1,0 +1,74 @@
+"""BASELINE config 4: dataset-scale sweep of N synthetic utterances (1..30 s), length-bucketed, sharded over
+the ranks of one box, mel_norms statistics all-reduced once at the end (NCCL).
+
+    python tools/sweep_bench.py [--utts 100000]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/sweep_bench.py
+
+Waveforms are never stored (137 GB for 100k clips): every batch is a view of one per-rank random pool
+(169 MB > L2), so the timed region is the hot path itself: forward (ragged, masks) + statistics.
+"""
+import argparse, json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np, torch
+import torch.distributed as dist
+from xtts_b200 import MelPlan
+from xtts_b200.sweep import MelSweep, norms_from_stats
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--utts", type=int, default=100000)
+args = ap.parse_args()
+world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=dev)
+plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
+               power=2.0, norm="slaney", device=dev)
+rng = np.random.default_rng(4321)
+lens = [int(round(22050 * u)) for u in rng.uniform(1.0, 30.0, size=args.utts)]
+sweep = MelSweep(plan, lens, bucket_seconds=2.0, max_clips=64, rank=rank, world_size=world)
+mine = sweep.my_buckets()
+pool = torch.rand(64 * 661500 + 4096, device=dev, generator=torch.Generator(device=dev).manual_seed(1234 + rank)) * 2 - 1
+len_dev = {b.indices: torch.tensor([lens[i] for i in b.indices], device=dev) for b in mine}
+
+
+def fetch(idx, max_len):
+    width = (max_len + 3) // 4 * 4                      # keep rows 16 B addressable
+    return pool[:len(idx) * width].view(len(idx), width)[:, :max_len], len_dev[tuple(idx)]
+
+
+def run():
+    return sweep.run_stats(fetch)
+
+
+full = list(sweep.owned[rank])
+sweep.owned[rank] = full[:3]
+run()                                                    # warm-up on three batches
+sweep.owned[rank] = full
+torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
+t0 = time.perf_counter()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+acc = run()                                              # includes the final all-reduce
+e1.record()
+torch.cuda.synchronize()
+ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+wall = time.perf_counter() - t0
+if world > 1:
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+plan.status()
+mean, std = norms_from_stats(acc)
+if rank == 0:
+    frames = int(acc[160].item())
+    audio = sum(lens) / 22050
+    my_frames = sum(b.frames for b in mine)
+    print(json.dumps({"workload": f"sweep_{args.utts}_utts_1-30s", "n_gpus": world, "ms": float(ms), "wall_s": wall,
+                      "audio_s_per_s": audio / (float(ms) * 1e-3), "frames_per_s": frames / (float(ms) * 1e-3),
+                      "frames_total": frames, "frames_expected": sum(1 + L // 256 for L in lens),
+                      "buckets": len(sweep.buckets), "rank0_frames_share": my_frames / frames,
+                      "mel_norms_head": [round(float(v), 5) for v in mean[:4]]}))
+if world > 1:
+    dist.destroy_process_group()

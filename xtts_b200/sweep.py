@@ -108,7 +108,8 @@ class MelSweep:
         self.plan = plan
         self.lengths = [int(v) for v in lengths]
         self.buckets = make_buckets(self.lengths, int(bucket_seconds * sample_rate), max_clips,
-                                    n_fft=plan.n_fft, hop=plan.hop, pad=plan.pad)
+                                    n_fft=plan.n_fft, hop=plan.hop, pad=plan.pad,
+                                    max_batch_samples=max_clips * 30 * sample_rate)
         self.owned = shard_buckets(self.buckets, world_size)
         self.rank, self.world_size = rank, world_size
 
