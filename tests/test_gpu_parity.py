@@ -277,3 +277,47 @@ def test_short_and_edge_heavy_clips(dev, v1):
         ref = orc.callsite_logmel(x, orc.V1, orc.default_mel_norms(80)).numpy()
         assert tuple(y.shape) == ref.shape, L
         assert np.abs(_np(y) - ref).max() <= TOL, L
+
+
+def test_constructor_variants_normalize_and_short_window(dev):
+    """normalize=True (spectrum / ||window||_2, torchaudio functional.py:139-140) and win_length < n_fft."""
+    from xtts_b200 import TorchMelSpectrogram
+    x = orc.synth("uniform", 3, 12000, 55)
+    for kw, cfg in ((dict(normalize=True), orc.MelConfig(normalized=True)),
+                    (dict(win_length=800), orc.MelConfig(win_length=800)),
+                    (dict(n_mel_channels=64, mel_fmax=7600, sampling_rate=16000),
+                     orc.MelConfig(n_mels=64, f_max=7600.0, sample_rate=16000))):
+        m = TorchMelSpectrogram(mel_norm_file=None, **kw)
+        y = m(torch.from_numpy(x).to(dev))
+        ref = orc.callsite_logmel(x, cfg, None).numpy()
+        assert tuple(y.shape) == ref.shape, kw
+        assert np.abs(_np(y) - ref).max() <= TOL, kw
+
+
+def test_many_tiny_clips_and_side_stream(dev, v1):
+    """3000 clips of 3 frames each (every frame is an edge frame; tiles span ~43 clips) on a non-default stream."""
+    x = orc.synth("gauss", 3000, 600, 77)
+    s = torch.cuda.Stream(dev)
+    xd = torch.from_numpy(x).to(dev)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(s):
+        y = v1(xd)
+    s.synchronize()
+    ref = orc.callsite_logmel(x, orc.V1, orc.default_mel_norms(80)).numpy()
+    assert tuple(y.shape) == ref.shape == (3000, 80, 3)
+    assert np.abs(_np(y) - ref).max() <= TOL
+
+
+def test_device_side_length_errors_are_reported(dev):
+    from xtts_b200 import MelPlan, _cabi
+    plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0,
+                   f_max=8000, power=2.0, norm="slaney", device=dev)
+    x = torch.zeros(2, 4000, device=dev)
+    plan.forward(x, torch.tensor([4000, 300], device=dev))       # 300 <= pad: cannot be reflect-padded
+    with pytest.raises(_cabi.MelError, match="length"):
+        plan.status()
+    plan.forward(x, torch.tensor([4000, 4000], device=dev), t_max=5)
+    with pytest.raises(_cabi.MelError, match="Tmax"):
+        plan.status()
+    plan.forward(x)
+    plan.status()

@@ -568,6 +568,7 @@ struct LogmelParams {
   const int64_t* lengths;     // [B] or null
   int64_t Lmax;
   int direct, pad;
+  int T_uniform;              // frames per clip when every clip is Lmax long (lengths == null), else 0
   const int64_t* frame_off;   // [B+1]
   const int32_t* n_frames;    // [B]
   int B;
@@ -719,12 +720,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         const int64_t g = (int64_t)tile * kTileM + q * 32 + lane;
         if (g < total_frames) {
           valid = true;
-          const int b = find_clip(P.frame_off, P.B, g);
-          const int t = (int)(g - P.frame_off[b]);
+          int b, t;
+          if (P.T_uniform) { b = (int)(g / P.T_uniform); t = (int)(g - (int64_t)b * P.T_uniform); }   // no memory traffic
+          else { b = find_clip(P.frame_off, P.B, g); t = (int)(g - P.frame_off[b]); }
           if (!P.direct) {
             base = (int32_t)((int64_t)b * P.src_stride + (int64_t)t * kHop);
           } else {
-            const int T = P.n_frames[b];
+            const int T = P.T_uniform ? P.T_uniform : P.n_frames[b];
             const int64_t L = P.lengths ? P.lengths[b] : P.Lmax;
             const int64_t s0 = (int64_t)t * kHop - P.pad;
             if (T <= 8 || s0 < 0) { edge = true; base = b * kEdgeClip + t * kHop; }
@@ -833,8 +835,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
       bool valid = g < total_frames;
       float* orow = nullptr;
       if (valid) {
-        const int b = find_clip(P.frame_off, P.B, g);
-        const int t = (int)(g - P.frame_off[b]);
+        int b, t;
+        if (P.T_uniform) { b = (int)(g / P.T_uniform); t = (int)(g - (int64_t)b * P.T_uniform); }
+        else { b = find_clip(P.frame_off, P.B, g); t = (int)(g - P.frame_off[b]); }
         valid = t < P.Tmax;
         orow = P.out + ((int64_t)b * P.Tmax + t) * P.n_mels;
       }
@@ -1100,6 +1103,10 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     LogmelParams P{};
     P.src = direct ? wav : w.xp; P.src_stride = direct ? row_stride : w.Lp; P.edge = w.edge;
     P.lengths = lengths; P.Lmax = Lmax; P.direct = direct; P.pad = p->cfg.pad;
+    {
+      const int64_t Tu = ttts_mel_frames(p, Lmax);
+      P.T_uniform = lengths ? 0 : (int)(Tu < Tmax ? Tu : Tmax);
+    }
     P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
     P.out = out; P.basis = p->d_basis; P.melw = p->d_melw; P.meladv = p->d_meladv; P.norms = p->d_norms;
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
