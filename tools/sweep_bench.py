@@ -27,7 +27,7 @@ plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n
                power=2.0, norm="slaney", device=dev)
 rng = np.random.default_rng(4321)
 lens = [int(round(22050 * u)) for u in rng.uniform(1.0, 30.0, size=args.utts)]
-sweep = MelSweep(plan, lens, bucket_seconds=2.0, max_clips=64, rank=rank, world_size=world)
+sweep = MelSweep(plan, lens, max_clips=64, rank=rank, world_size=world)   # length-sorted batches of 64
 mine = sweep.my_buckets()
 pool = torch.rand(64 * 661500 + 4096, device=dev, generator=torch.Generator(device=dev).manual_seed(1234 + rank)) * 2 - 1
 len_dev = {b.indices: torch.tensor([lens[i] for i in b.indices], device=dev) for b in mine}

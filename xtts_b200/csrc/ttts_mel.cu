@@ -4,8 +4,10 @@
 // torchaudio/torch.stft/matmul, the whole chain reflect-pad -> frame -> Hann -> rDFT -> |.|^p ->
 // mel filterbank -> log(clamp) -> / mel_norms with five kernels:
 //
-//   k_prep    lengths -> n_frames (torch.stft frame count) + exclusive prefix (frame -> clip map)
-//   k_pad     per-clip reflect padding into a workspace signal (128-bit coalesced loads/stores)
+//   k_prep    block 0: lengths -> n_frames (torch.stft frame count) + exclusive prefix (frame -> clip map);
+//             blocks 1..B: per-clip edge buffers (the few frames that touch the reflect padding), zeros for padded
+//             output frames, padding mask
+//   k_pad     full per-clip reflect padding into the workspace (only for inputs that are not 16 B addressable)
 //   k_logmel  the fused hot kernel (persistent, warp-specialised, one CTA per SM):
 //               loader warp     cp.async 16 B gathers of the overlapping hop windows -> smem ring
 //               converter warps even/odd fold  E[n]=f[n]+f[N-n], O[n]=f[n]-f[N-n]  (halves K),
@@ -445,16 +447,19 @@ __device__ __forceinline__ long long clip_frames(long long L, long long Lmax, in
   return T;
 }
 
-__device__ void edge_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
-                          int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, int b);
+__device__ void clip_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
+                          int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, float* __restrict__ out, int n_mels,
+                          uint8_t* __restrict__ mask, int b);
 
-// Block 0: frame counts + prefix.  Blocks 1..B (only when `edge` is given): the edge buffer of clip blockIdx.x-1.
+// Block 0: frame counts + prefix.  Blocks 1..B: per-clip side work of clip blockIdx.x-1 -- its edge buffer (when `edge`
+// is given), zeros for its padded output frames (ragged batches) and its row of the padding mask (when `mask` is given).
 __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, int64_t row_stride, float* __restrict__ edge,
+                                               float* __restrict__ out, int n_mels, uint8_t* __restrict__ mask,
                                                const int64_t* __restrict__ lengths, int B, int64_t Lmax, int pad,
                                                int Tmax, int32_t* __restrict__ n_frames,
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
                                                int32_t* __restrict__ status) {
-  if (blockIdx.x > 0) { edge_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, blockIdx.x - 1); return; }
+  if (blockIdx.x > 0) { clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, blockIdx.x - 1); return; }
   __shared__ long long part[1024];
   const int tid = threadIdx.x;
   if (tid == 0) *status = 0;
@@ -525,36 +530,37 @@ __global__ void __launch_bounds__(256) k_pad(const float* __restrict__ wav, int6
 // <= 3 frames of every clip, or the whole clip when it has <= 8 frames); every other frame is read
 // straight from the caller's waveform by k_logmel.  edge[b] = A: padded[0, 2880) | B: padded[256 (T-4), +1792)
 // ------------------------------------------------------------------------------------------
-__device__ void edge_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
-                          int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, int b) {
+__device__ void clip_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
+                          int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, float* __restrict__ out, int n_mels,
+                          uint8_t* __restrict__ mask, int b) {
   const int64_t L = lengths ? lengths[b] : Lmax;
   int err = 0;
   const int T = (int)clip_frames(L, Lmax, pad, Tmax, &err);
-  const float* __restrict__ src = wav + (int64_t)b * row_stride;
-  float* __restrict__ dst = edge + (int64_t)b * kEdgeClip;
-  const bool okL = T > 0 && err != 1;
-  const int64_t startB = (int64_t)kHop * (T - 4);
-  for (int i = threadIdx.x; i < kEdgeClip; i += blockDim.x) {
-    const bool inB = i >= kEdgeA;
-    int64_t s = (inB ? startB + (i - kEdgeA) : (int64_t)i) - pad;
-    float v = 0.f;
-    if (okL && (!inB || T > 8) && s >= -(int64_t)pad && s < L + pad) {
-      if (s < 0) s = -s;
-      if (s >= L) s = 2 * (L - 1) - s;
-      v = __ldg(src + s);
+  if (edge) {
+    const float* __restrict__ src = wav + (int64_t)b * row_stride;
+    float* __restrict__ dst = edge + (int64_t)b * kEdgeClip;
+    const bool okL = T > 0 && err != 1;
+    const int64_t startB = (int64_t)kHop * (T - 4);
+    for (int i = threadIdx.x; i < kEdgeClip; i += blockDim.x) {
+      const bool inB = i >= kEdgeA;
+      int64_t s = (inB ? startB + (i - kEdgeA) : (int64_t)i) - pad;
+      float v = 0.f;
+      if (okL && (!inB || T > 8) && s >= -(int64_t)pad && s < L + pad) {
+        if (s < 0) s = -s;
+        if (s >= L) s = 2 * (L - 1) - s;
+        v = __ldg(src + s);
+      }
+      dst[i] = v;
     }
-    dst[i] = v;
   }
-}
-
-// ------------------------------------------------------------------------------------------
-// k_mask: make_pad_mask (ttts/utils/utils.py:77-103): mask[b][t] = t >= n_frames[b]
-// ------------------------------------------------------------------------------------------
-__global__ void k_mask(const int32_t* __restrict__ n_frames, int B, int Tmax, uint8_t* __restrict__ mask) {
-  const int64_t total = (int64_t)B * Tmax;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int b = (int)(i / Tmax), t = (int)(i % Tmax);
-    mask[i] = t >= n_frames[b] ? 1 : 0;
+  if (out && lengths) {          // collate contract (ttts/gpt/dataset.py:116-117): frames t >= n_frames[b] are 0.0
+    float* __restrict__ z = out + ((int64_t)b * Tmax + T) * n_mels;
+    const int64_t n = (int64_t)(Tmax - T) * n_mels;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) z[i] = 0.f;
+  }
+  if (mask) {                    // make_pad_mask (ttts/utils/utils.py:77-103)
+    uint8_t* __restrict__ mrow = mask + (int64_t)b * Tmax;
+    for (int t = threadIdx.x; t < Tmax; t += blockDim.x) mrow[t] = t >= T ? 1 : 0;
   }
 }
 
@@ -1085,18 +1091,13 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   // the reflect padding go through a small edge buffer.  Otherwise (and for k_simt) the clips are padded
   // into the workspace first.
   const bool direct = impl == Impl::Tcgen05 && vec_ok && (int64_t)B * row_stride < ((int64_t)1 << 31);
-  k_prep<<<direct ? B + 1 : 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, lengths, B, Lmax,
-                                                  p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.status);
+  k_prep<<<B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
+                                     p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.status);
   ++g_launches;
   if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
     dim3 grid((unsigned)((vecs + 255) / 256 > 4096 ? 4096 : (vecs + 255) / 256), (unsigned)B);
     k_pad<<<grid, 256, 0, stream>>>(wav, row_stride, lengths, Lmax, p->cfg.pad, w.xp, w.Lp, vec_ok);
-    ++g_launches;
-  }
-  if (lengths) CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)B * Tmax * p->cfg.n_mels * sizeof(float), stream));
-  if (mask) {
-    k_mask<<<p->num_sms * 4, 256, 0, stream>>>(w.n_frames, B, Tmax, mask);
     ++g_launches;
   }
   if (impl == Impl::Tcgen05) {

@@ -101,9 +101,13 @@ class MelSweep:
     ``fetch(indices, max_len) -> (wav[B, max_len] float32 CUDA tensor, lengths[B] int64)`` supplies a batch;
     ``sink(indices, mel[B, n_mels, T], n_frames[B])`` consumes results (the reference's per-file
     ``torch.save(mel, f'{wav}.mel.pth')``, mel_extract.py:27); ``done(index) -> bool`` is the reference's
-    skip-if-exists resume rule (mel_extract.py:10-12)."""
+    skip-if-exists resume rule (mel_extract.py:10-12).
 
-    def __init__(self, plan, lengths: Sequence[int], *, bucket_seconds: float = 2.0, sample_rate: int = 22050,
+    ``bucket_seconds`` bounds the length spread inside a batch.  It only bounds MEMORY (the padded input tensor):
+    the kernel indexes frames of all clips in one flat space, so padding costs no compute, and larger batches fill
+    the 148 SMs better.  The default (30 s) therefore means "length-sorted batches of ``max_clips`` clips"."""
+
+    def __init__(self, plan, lengths: Sequence[int], *, bucket_seconds: float = 30.0, sample_rate: int = 22050,
                  max_clips: int = 64, rank: int = 0, world_size: int = 1):
         self.plan = plan
         self.lengths = [int(v) for v in lengths]
