@@ -38,7 +38,9 @@ extern "C" {
 /* Constructor arguments of the reference modules, already resolved to numbers.
  *   V1  TorchMelSpectrogram.__init__      ttts/utils/utils.py:487-502      (n_mels 80, pad 512, power 2, clamp 1e-5)
  *   V2  MelSpectrogramFeatures.__init__   ttts/vocoder/feature_extractors.py:74-91 + safe_log modules.py:194-205
- *                                          (n_mels 100, pad 512 | 384 for padding="same", power 1, clamp 1e-7)   */
+ *                                          (n_mels 100, pad 512 | 384 for padding="same", power 1, clamp 1e-7)
+ *   V3  mel_spectrogram() / MelSpectrogramFeatures1   ttts/vocoder/feature_extractors.py:27-53,102-121
+ *                                          (librosa Slaney filterbank, pad 384, power 1 with eps 1e-9, clamp 1e-5) */
 typedef struct ttts_mel_config {
   int32_t n_fft;       /* 1024 (the only size built this round)                                  */
   int32_t hop;         /* 256                                                                    */
@@ -47,6 +49,8 @@ typedef struct ttts_mel_config {
   float   power;       /* 2.0 (|X|^2) or 1.0 (|X|)                                                */
   float   clamp;       /* floor applied before the natural log                                   */
   float   spec_scale;  /* scales the complex spectrum: 1, or 1/||window||_2 for normalized=True  */
+  float   power_eps;   /* power == 1 only: magnitude = sqrt(re^2 + im^2 + power_eps); 1e-9 for the   */
+                       /* HiFi-GAN style mel_spectrogram(), feature_extractors.py:46; else 0        */
 } ttts_mel_config;
 
 typedef struct ttts_mel_plan ttts_mel_plan;

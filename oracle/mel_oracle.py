@@ -63,6 +63,8 @@ class MelConfig:
     clamp: float = 1e-5
     center: bool = True
     pre_pad: int = 0            # "same" padding of V2: reflect-pad (win-hop)//2 first, center=False
+    power_eps: float = 0.0      # V3: magnitude = sqrt(re^2 + im^2 + 1e-9), feature_extractors.py:46
+    librosa_fb: bool = False    # V3: librosa.filters.mel (Slaney scale + norm) instead of torchaudio's fbanks
 
     @property
     def n_freqs(self) -> int:
@@ -82,6 +84,11 @@ V1 = MelConfig()
 V2 = MelConfig(sample_rate=24000, n_mels=100, f_max=None, power=1.0, norm=None, clamp=1e-7)
 V2_SAME = MelConfig(sample_rate=24000, n_mels=100, f_max=None, power=1.0, norm=None, clamp=1e-7,
                     center=False, pre_pad=(1024 - 256) // 2)
+# V3 = mel_spectrogram() / MelSpectrogramFeatures1 defaults, ttts/vocoder/feature_extractors.py:27-53,102-121.
+# PARITY UNPINNED for this row: librosa (the source of its filterbank) is not installed here, so the filterbank is
+# restated from librosa's published algorithm (melscale_fbanks64 with the Slaney scale) and no golden could be minted.
+V3 = MelConfig(sample_rate=24000, n_mels=80, f_max=8000.0, power=1.0, norm="slaney", mel_scale="slaney", clamp=1e-5,
+               center=False, pre_pad=(1024 - 256) // 2, power_eps=1e-9, librosa_fb=True)
 
 
 def default_mel_norms(n_mels: int = 80) -> np.ndarray:
@@ -197,7 +204,7 @@ def restated_stages(x: np.ndarray, cfg: MelConfig = V1, fb: Optional[np.ndarray]
         w = w / math.sqrt(float((w ** 2).sum()))
     X = np.fft.rfft(frames * w[None, :], axis=-1)
     mag2 = X.real ** 2 + X.imag ** 2
-    spec = mag2 if cfg.power == 2.0 else np.sqrt(mag2) ** cfg.power
+    spec = mag2 if cfg.power == 2.0 else np.sqrt(mag2 + cfg.power_eps) ** cfg.power
     fb = melscale_fbanks64(cfg) if fb is None else np.asarray(fb, dtype=np.float64)
     mel = spec @ fb
     logmel = np.log(np.maximum(mel, cfg.clamp))
@@ -261,6 +268,15 @@ def callsite_logmel(wav, cfg: MelConfig = V1, mel_norms=None):
     if x.dim() == 3:
         x = x.squeeze(1)
     assert x.dim() == 2
+    if cfg.librosa_fb:
+        # mel_spectrogram(), feature_extractors.py:40-51
+        basis = torch.from_numpy(melscale_fbanks64(cfg).T.astype(np.float32))          # librosa_mel_fn(...)
+        y = torch.nn.functional.pad(x.unsqueeze(1), (cfg.pre_pad, cfg.pre_pad), mode="reflect").squeeze(1)
+        spec = torch.stft(y, cfg.n_fft, hop_length=cfg.hop, win_length=cfg.win_length,
+                          window=torch.hann_window(cfg.win_length), center=False, pad_mode="reflect",
+                          normalized=False, onesided=True, return_complex=True)
+        spec = torch.sqrt(torch.view_as_real(spec).pow(2).sum(-1) + cfg.power_eps)
+        return torch.log(torch.clamp(torch.matmul(basis, spec), min=cfg.clamp))
     if cfg.pre_pad:
         x = torch.nn.functional.pad(x, (cfg.pre_pad, cfg.pre_pad), mode="reflect")
     mel = _callsite_transform(cfg)(x)

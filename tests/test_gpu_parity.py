@@ -321,3 +321,17 @@ def test_device_side_length_errors_are_reported(dev):
         plan.status()
     plan.forward(x)
     plan.status()
+
+
+def test_v3_librosa_style_mel_spectrogram(dev):
+    """feature_extractors.py:27-53,102-121 (mel_type == "librosa"); oracle for this row is unpinned (see oracle header)."""
+    from xtts_b200 import MelSpectrogramFeatures1, mel_spectrogram
+    m = MelSpectrogramFeatures1()
+    for L in (24000, 5000, 1024, 777):
+        x = orc.synth("uniform", 2, L, 900 + L)
+        y = m(torch.from_numpy(x).to(dev))
+        ref = orc.callsite_logmel(x, orc.V3).numpy()
+        assert tuple(y.shape) == ref.shape == (2, 80, L // 256)
+        assert np.abs(_np(y) - ref).max() <= TOL, L
+    y2 = mel_spectrogram(torch.from_numpy(x).to(dev), 1024, 80, 24000, 256, 1024, 0, 8000, center=False)
+    assert torch.equal(y, y2)

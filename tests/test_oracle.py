@@ -124,3 +124,19 @@ def test_mel_stats():
     assert acc[160] == 28
     assert np.allclose(acc[:80], lm[0].sum(1) + lm[1, :, :7].sum(1) + lm[2, :, :1].sum(1))
     assert np.allclose(orc.norms_from_stats(acc), acc[:80] / 28, rtol=1e-6)
+
+
+def test_v3_layers_agree_and_filterbank_restatement():
+    """V3 (mel_spectrogram, feature_extractors.py:27-53): parity UNPINNED (no librosa here) -- the two oracle layers
+    and the product's librosa_mel restatement must at least agree with each other and with torchaudio's Slaney bank."""
+    import torchaudio
+    from xtts_b200.filterbank import librosa_mel
+    fb = librosa_mel(24000, 1024, 80, 0, 8000)
+    assert fb.shape == (80, 513) and fb.dtype == torch.float32
+    assert np.abs(fb.numpy() - orc.melscale_fbanks64(orc.V3).T).max() < 1e-7
+    ta = torchaudio.functional.melscale_fbanks(513, 0.0, 8000.0, 80, 24000, "slaney", "slaney").t()
+    assert float((fb - ta).abs().max()) < 2e-7
+    x = orc.synth("uniform", 2, 6000, 12)
+    a = orc.callsite_logmel(x, orc.V3).numpy()
+    assert a.shape == (2, 80, 6000 // 256)
+    assert np.abs(orc.restated_logmel(x, orc.V3) - a).max() <= 5e-5

@@ -4,8 +4,8 @@ Only the hot path: ``TorchMelSpectrogram`` / ``MelSpectrogramFeatures`` / ``dvae
 ``make_pad_mask`` (host mirror of the reference interface, ``mel.py``) on top of
 ``libttts_mel.so`` (``csrc/ttts_mel.cu`` behind the C ABI of ``include/ttts_mel.h``).
 """
-from .mel import (DEFAULT_MEL_NORM_FILE, MelPlan, MelSpectrogramFeatures, TorchMelSpectrogram,
-                  dvae_wav_to_mel, make_pad_mask)
+from .mel import (DEFAULT_MEL_NORM_FILE, MelPlan, MelSpectrogramFeatures, MelSpectrogramFeatures1,
+                  TorchMelSpectrogram, dvae_wav_to_mel, make_pad_mask, mel_spectrogram)
 
-__all__ = ["DEFAULT_MEL_NORM_FILE", "MelPlan", "MelSpectrogramFeatures", "TorchMelSpectrogram",
-           "dvae_wav_to_mel", "make_pad_mask"]
+__all__ = ["DEFAULT_MEL_NORM_FILE", "MelPlan", "MelSpectrogramFeatures", "MelSpectrogramFeatures1",
+           "TorchMelSpectrogram", "dvae_wav_to_mel", "make_pad_mask", "mel_spectrogram"]

@@ -18,7 +18,7 @@ OK, EINVAL, ECUDA, ENOMEM, EDEVICE = 0, -1, -2, -3, -4
 
 class MelConfig(Structure):
     _fields_ = [("n_fft", c_int32), ("hop", c_int32), ("n_mels", c_int32), ("pad", c_int32),
-                ("power", c_float), ("clamp", c_float), ("spec_scale", c_float)]
+                ("power", c_float), ("clamp", c_float), ("spec_scale", c_float), ("power_eps", c_float)]
 
 
 class MelError(RuntimeError):

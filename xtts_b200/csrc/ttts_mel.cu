@@ -144,6 +144,8 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
     return fail(TTTS_MEL_EINVAL, "pad %d must be a multiple of 4 in [0,%d]", cfg->pad, kNfft / 2);
   if (!(cfg->power == 1.0f || cfg->power == 2.0f)) return fail(TTTS_MEL_EINVAL, "power must be 1 or 2");
   if (!(cfg->clamp > 0.f)) return fail(TTTS_MEL_EINVAL, "clamp must be > 0");
+  if (!(cfg->power_eps >= 0.f) || (cfg->power == 2.0f && cfg->power_eps != 0.f))
+    return fail(TTTS_MEL_EINVAL, "power_eps must be >= 0 and is only defined for power == 1");
   const int N = kNfft, nfreq = N / 2 + 1, nm = cfg->n_mels;
 
   // The even/odd fold needs w[n] == w[N-n] and contributes nothing at n = 0 only if w[0] == 0.
@@ -585,7 +587,7 @@ struct LogmelParams {
   const uint32_t* meladv;     // [nbt/16]
   const float* norms;         // [n_mels] or null
   int passes, nb, nbt, n_mels;
-  float clamp;
+  float clamp, power_eps;
   int power_is_1;
   int32_t* status;
   float* dbg_reim;            // optional [total_frames][2*nbt]
@@ -870,7 +872,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
             }
             const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
             float pw = fmaf(a, a, bq * bq);
-            if (kPower1) pw = sqrtf(pw);
+            if (kPower1) pw = sqrtf(pw + P.power_eps);
             run_lo = fmaf(h ? w2.z : w2.x, pw, run_lo);
             run_hi = fmaf(h ? w2.w : w2.y, pw, run_hi);
           }
@@ -962,7 +964,7 @@ __global__ void __launch_bounds__(kSimtThreads) k_simt(const float* __restrict__
                                                        int B, int Tmax, float* __restrict__ out,
                                                        const float* __restrict__ cosf_, const float* __restrict__ sinf__,
                                                        const float* __restrict__ fb, const float* __restrict__ norms,
-                                                       int nbt, int n_mels, float clamp, int power_is_1) {
+                                                       int nbt, int n_mels, float clamp, int power_is_1, float power_eps) {
   extern __shared__ float sm[];
   float* sE = sm;                                  // [F][512]
   float* sO = sE + kSimtFrames * kKfold;           // [F][512]
@@ -1003,7 +1005,7 @@ __global__ void __launch_bounds__(kSimtThreads) k_simt(const float* __restrict__
 #pragma unroll
     for (int f = 0; f < kSimtFrames; ++f) {
       float pw = fmaf(re[f], re[f], im[f] * im[f]);
-      if (power_is_1) pw = sqrtf(pw);
+      if (power_is_1) pw = sqrtf(pw + power_eps);
       sP[f * nbt + i] = pw;
     }
   }
@@ -1111,7 +1113,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
     P.out = out; P.basis = p->d_basis; P.melw = p->d_melw; P.meladv = p->d_meladv; P.norms = p->d_norms;
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
-    P.clamp = p->cfg.clamp; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim; P.exp_flags = g_exp_flags;
+    P.clamp = p->cfg.clamp; P.power_eps = p->cfg.power_eps; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim; P.exp_flags = g_exp_flags;
     const size_t smem = logmel_smem_bytes(p);
     void (*kern)(const LogmelParams) =
         dbg_reim ? (P.power_is_1 ? k_logmel<true, true> : k_logmel<false, true>)
@@ -1133,7 +1135,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
       configured = smem;
     }
     k_simt<<<blocks, kSimtThreads, smem, stream>>>(w.xp, w.Lp, w.frame_off, B, Tmax, out, p->d_cosf, p->d_sinf, p->d_fb,
-                                                  p->d_norms, p->nbt, p->cfg.n_mels, p->cfg.clamp, p->cfg.power == 1.0f);
+                                                  p->d_norms, p->nbt, p->cfg.n_mels, p->cfg.clamp, p->cfg.power == 1.0f, p->cfg.power_eps);
     ++g_launches;
   }
   CUDA_TRY(cudaGetLastError());

@@ -71,3 +71,40 @@ def analysis_window(n_fft: int, win_length: Optional[int]) -> torch.Tensor:
     out = torch.zeros(n_fft)
     out[left:left + win_length] = w
     return out
+
+
+def librosa_mel(sr: int, n_fft: int, n_mels: int, fmin: float = 0.0, fmax: Optional[float] = None) -> torch.Tensor:
+    """``librosa.filters.mel(sr=, n_fft=, n_mels=, fmin=, fmax=)`` with its defaults (Slaney mel scale,
+    ``norm='slaney'``, float32 result of an fp64 computation), restated from the published algorithm because
+    librosa is not installed here.  The reference calls it in ``mel_spectrogram()``
+    (ttts/vocoder/feature_extractors.py:36-37).  Returns ``[n_mels, 1 + n_fft//2]`` float32."""
+    import numpy as np
+    fmax = float(sr) / 2 if fmax is None else float(fmax)
+    fftfreqs = np.linspace(0.0, float(sr) / 2, 1 + n_fft // 2)            # librosa.fft_frequencies
+
+    def hz_to_mel_slaney(f):
+        f = np.asanyarray(f, dtype=np.float64)
+        f_sp = 200.0 / 3
+        mels = f / f_sp
+        min_log_hz, logstep = 1000.0, np.log(6.4) / 27.0
+        min_log_mel = min_log_hz / f_sp
+        return np.where(f >= min_log_hz, min_log_mel + np.log(np.maximum(f, 1e-30) / min_log_hz) / logstep, mels)
+
+    def mel_to_hz_slaney(m):
+        m = np.asanyarray(m, dtype=np.float64)
+        f_sp = 200.0 / 3
+        min_log_hz, logstep = 1000.0, np.log(6.4) / 27.0
+        min_log_mel = min_log_hz / f_sp
+        return np.where(m >= min_log_mel, min_log_hz * np.exp(logstep * (m - min_log_mel)), f_sp * m)
+
+    mel_f = mel_to_hz_slaney(np.linspace(hz_to_mel_slaney(fmin), hz_to_mel_slaney(fmax), n_mels + 2))
+    fdiff = np.diff(mel_f)
+    ramps = mel_f[:, None] - fftfreqs[None, :]
+    weights = np.zeros((n_mels, 1 + n_fft // 2), dtype=np.float64)
+    for i in range(n_mels):
+        lower = -ramps[i] / fdiff[i]
+        upper = ramps[i + 2] / fdiff[i + 1]
+        weights[i] = np.maximum(0, np.minimum(lower, upper))
+    enorm = 2.0 / (mel_f[2:n_mels + 2] - mel_f[:n_mels])
+    weights *= enorm[:, None]
+    return torch.from_numpy(weights.astype(np.float32))

@@ -5,6 +5,7 @@ behaviour; file:line in /root/reference):
 
 * ``TorchMelSpectrogram``      ttts/utils/utils.py:486-522           (V1, 22.05 kHz / 80 mel / power 2)
 * ``MelSpectrogramFeatures``   ttts/vocoder/feature_extractors.py:73-99 (V2, 24 kHz / 100 mel / power 1)
+* ``MelSpectrogramFeatures1`` / ``mel_spectrogram``  ttts/vocoder/feature_extractors.py:27-53,102-121 (V3, librosa mel)
 * ``dvae_wav_to_mel``          ttts/vqvae/xtts_dvae.py:28-49
 * ``make_pad_mask``            ttts/utils/utils.py:77-103
 
@@ -27,7 +28,7 @@ import torch
 from torch import nn
 
 from . import _cabi
-from .filterbank import analysis_window, melscale_fbanks
+from .filterbank import analysis_window, librosa_mel, melscale_fbanks
 
 DEFAULT_MEL_NORM_FILE = os.path.join(os.path.dirname(os.path.realpath(__file__)), "data", "mel_norms.pth")
 
@@ -46,7 +47,8 @@ class MelPlan:
     def __init__(self, *, sample_rate: int, n_fft: int, hop_length: int, win_length: Optional[int],
                  n_mels: int, f_min: float, f_max: Optional[float], power: float, norm: Optional[str],
                  mel_scale: str = "htk", normalized: bool = False, clamp: float = 1e-5,
-                 center: bool = True, pre_pad: int = 0, device: Union[str, torch.device, int] = "cuda"):
+                 center: bool = True, pre_pad: int = 0, power_eps: float = 0.0,
+                 fb: Optional[torch.Tensor] = None, device: Union[str, torch.device, int] = "cuda"):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("MelPlan needs a CUDA device (sm_100a); there is no CPU fallback")
@@ -56,13 +58,15 @@ class MelPlan:
         self.pad = self.n_fft // 2 if center else int(pre_pad)
         self.power, self.clamp = float(power), float(clamp)
         f_max = float(f_max) if f_max is not None else float(sample_rate // 2)
-        self.fb = melscale_fbanks(self.n_fft // 2 + 1, float(f_min), f_max, self.n_mels, int(sample_rate),
-                                  norm, mel_scale).contiguous()
+        if fb is None:
+            fb = melscale_fbanks(self.n_fft // 2 + 1, float(f_min), f_max, self.n_mels, int(sample_rate), norm, mel_scale)
+        self.fb = fb.to(torch.float32).contiguous()          # [n_freqs, n_mels]
         self.window = analysis_window(self.n_fft, win_length).contiguous()
         spec_scale = 1.0
         if normalized:      # torchaudio functional.py:139-140: spec_f /= window.pow(2).sum().sqrt()
             spec_scale = 1.0 / math.sqrt(float(self.window.pow(2.0).sum()))
-        cfg = _cabi.MelConfig(self.n_fft, self.hop, self.n_mels, self.pad, self.power, self.clamp, spec_scale)
+        cfg = _cabi.MelConfig(self.n_fft, self.hop, self.n_mels, self.pad, self.power, self.clamp, spec_scale,
+                              float(power_eps))
         handle = ctypes.c_void_p()
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().ttts_mel_plan_create(ctypes.byref(cfg), self.fb.data_ptr(),
@@ -280,6 +284,47 @@ class MelSpectrogramFeatures(_MelModuleBase):
 
     def forward(self, audio, lengths=None, **kwargs):
         return self._run(audio, lengths)
+
+
+_V3_PLANS = {}
+
+
+def mel_spectrogram(y, n_fft, num_mels, sampling_rate, hop_size, win_size, fmin, fmax, center=False):
+    """ttts/vocoder/feature_extractors.py:27-53: reflect-pad (n_fft-hop)/2, STFT with center=False,
+    sqrt(re^2+im^2+1e-9), librosa (Slaney) mel basis, log(clamp(., 1e-5)).  Returns [B, num_mels, L // hop]."""
+    if center:
+        raise NotImplementedError("mel_spectrogram(center=True) is not used by the reference and is not built")
+    if not y.is_cuda:
+        raise RuntimeError("mel_spectrogram (xtts_b200) runs on CUDA sm_100a only; there is no CPU fallback")
+    dev = y.device if y.device.index is not None else torch.device("cuda", torch.cuda.current_device())
+    key = (n_fft, num_mels, sampling_rate, hop_size, win_size, fmin, fmax, dev.index)
+    plan = _V3_PLANS.get(key)
+    if plan is None:
+        fb = librosa_mel(sampling_rate, n_fft, num_mels, fmin, fmax).t().contiguous()
+        plan = _V3_PLANS[key] = MelPlan(sample_rate=sampling_rate, n_fft=n_fft, hop_length=hop_size, win_length=win_size,
+                                       n_mels=num_mels, f_min=fmin, f_max=fmax, power=1.0, norm=None, clamp=1e-5,
+                                       center=False, pre_pad=int((n_fft - hop_size) / 2), power_eps=1e-9, fb=fb, device=dev)
+    if y.dim() == 3:
+        y = y.squeeze(1)
+    mel, _, _ = plan.forward(y.float())
+    return mel.transpose(1, 2)
+
+
+class MelSpectrogramFeatures1(nn.Module):
+    """ttts/vocoder/feature_extractors.py:102-121 (selected by mel_type == "librosa", ttts/vqvae/dataset.py:27-28)."""
+
+    def __init__(self, sample_rate=24000, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, mel_fmin=0,
+                 mel_fmax=8000, normalize=False, padding="center"):
+        super().__init__()
+        if padding not in ["center", "same"]:
+            raise ValueError("Padding must be 'center' or 'same'.")
+        self.padding = padding
+        self.sampling_rate, self.n_fft, self.num_mels = sample_rate, n_fft, n_mels
+        self.hop_size, self.win_size, self.fmin, self.fmax = hop_length, win_length, mel_fmin, mel_fmax
+
+    def forward(self, audio, **kwargs):
+        return mel_spectrogram(audio, self.n_fft, self.num_mels, self.sampling_rate, self.hop_size, self.win_size,
+                               self.fmin, self.fmax, center=False)
 
 
 _DVAE_MODULES = {}
