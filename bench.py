@@ -38,6 +38,13 @@ def frames_of(L: int) -> int:
     return 1 + L // 256
 
 
+def config_dict(world: int) -> dict:
+    return {"workload": WORKLOAD, "clips_per_step_per_gpu": B_CLIPS, "clip_seconds": 10,
+            "frames_per_step_per_gpu": B_CLIPS * frames_of(CLIP_LEN),
+            "sharding": f"dp{world}: one batch per rank, no data-path collective",
+            "l2": f"inputs rotate over {ROTATE} distinct batches (226 MB > 126 MB L2)"}
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
@@ -124,7 +131,7 @@ def run_reference(args):
         "impl": "reference", "metric": "log-mel audio-seconds/sec", "value": val, "unit": "audio-s/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec_per_step * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "clips_per_step": B_CLIPS, "clip_seconds": 10, "frames_per_step": B_CLIPS * frames_of(CLIP_LEN)},
+        "config": config_dict(args.gpus),
         "frames_per_s": val * SR / 256.0,
         "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port",
                          "sample": f"{args.steps} steps x one full 64x10 s batch through the reference's call sequence "
@@ -283,9 +290,7 @@ def run_ours(args):
             "metric": "log-mel audio-seconds/sec", "value": value, "unit": "audio-s/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "tf32x3(f32 accumulate)", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "clips_per_step_per_gpu": B_CLIPS, "clip_seconds": 10,
-                       "frames_per_step_per_gpu": frames_step, "sharding": f"dp{world}: one batch per rank, no data-path collective",
-                       "l2": f"inputs rotate over {ROTATE} distinct batches (226 MB > 126 MB L2)"},
+            "config": config_dict(world),
             "frames_per_s": value * SR / 256.0,
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "audio-s/s", "h2d_bytes_per_step": B_CLIPS * CLIP_LEN * 4,
