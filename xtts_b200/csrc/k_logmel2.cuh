@@ -1,0 +1,489 @@
+// k_logmel2.cuh -- second-generation fused log-mel kernel ("double fold"), included by ttts_mel.cu.
+//
+// Same contract as k_logmel (ttts_mel.cu) and the same reference chain (ttts/utils/utils.py:509-522 via
+// torchaudio MelSpectrogram / torch.stft), but the DFT-GEMM contracts over K = 256 (+1) instead of 512:
+//
+//   first fold (as k_logmel)    E'[n] = w[n] (f[n] + f[N-n]),  O'[n] = w[n] (f[n] - f[N-n]),   n = 1..512
+//   second fold (new)           cos(2 pi k (512-n)/N) = (-1)^k cos(2 pi k n/N),  sin(..(512-n)..) = -(-1)^k sin(..n..)
+//        even k:  Re[k] = sum_{n=1..256} (E'[n] + E'[512-n]) cos(th_kn) + E'[512]
+//                 Im[k] = sum_{n=1..256} (O'[n] - O'[512-n]) sin(th_kn)
+//        odd  k:  Re[k] = sum_{n=1..256} (E'[n] - E'[512-n]) cos(th_kn) - E'[512]
+//                 Im[k] = sum_{n=1..256} (O'[n] + O'[512-n]) sin(th_kn)
+//   (the n = 256 slot pairs with itself: its partner weight is 0).  Even and odd bins are separate accumulator
+//   passes with different A operands, so tensor work, basis bytes and basis L2 traffic all halve; the window moves
+//   from the basis into the converter (two FMULs per tap), the basis is the pure TF32 hi/lo split of cos/sin.
+//   The centre tap E'[512] = w[512] f[512] is a 33rd k-step that carries one live column (basis +-1).
+//
+// Pipeline differences from k_logmel:
+//   * converters work at k-step granularity: kSets sets x 4 lane quarters; set s owns A stage s and every k-step with
+//     sequence number == s (mod kSets).  Per k-step a warp stages, for its 32 rows, 34 "slots" of 20 floats:
+//     slot v = [ frame v's taps 8ks..8ks+11 | frame v-2's taps 1016-8ks..1023-8ks ].  Because hop = N/4, row r's
+//     four windows are slot r (a = f[n], c = f[512-n]) and slot r+2 (d = f[512+n], b = f[N-n]): every sample is
+//     staged once per pass instead of twice.  This needs the 32 rows of a warp to be consecutive frames of ONE clip,
+//     so clips are laid out in groups of 32 frames (the last group of a clip is partly empty).
+//   * the epilogue restarts its running-filter scan per parity and adds the second parity onto the parked sums.
+#pragma once
+
+namespace f2 {
+
+constexpr int kSets = 3;                         // converter sets == A-operand TMEM stages
+constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
+constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
+constexpr int kSlotFloats = 20;                  // 12 forward taps + 8 mirrored taps; 80 B pitch: conflict-free LDS.128
+constexpr int kStageBytes = kSlots * kSlotFloats * 4;
+constexpr int kDepth = 2;                        // raw-audio stages per converter warp
+constexpr int kPieces = kSlots * 5;              // 16 B pieces per stage
+constexpr int kPieceIters = (kPieces + 31) / 32;
+constexpr int kConvWarps2 = 4 * kSets;
+constexpr int kWarpConv02 = 4;
+constexpr int kWarpEpi02 = kWarpConv02 + kConvWarps2;
+constexpr int kThreads2 = (kWarpEpi02 + 4) * 32;
+constexpr int kBStages2 = 4;                      // basis ring depth
+constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
+constexpr int kGroup = 32;                       // frames per group (one converter / epilogue warp)
+
+struct Params {
+  const float* src;           // direct: the caller's waveform [B][src_stride]; else workspace xp [B][Lp]
+  int64_t src_stride;
+  const float* edge;          // [B][kEdgeClip] (direct mode)
+  const int64_t* lengths;     // [B] or null
+  int64_t Lmax;
+  int direct, pad;
+  int T_uniform, G_uniform;   // frames / groups per clip when lengths == null, else 0
+  const int64_t* group_off;   // [B+1] exclusive prefix of ceil(n_frames / 32)
+  const int64_t* frame_off;   // [B+1] (debug dump only)
+  const int32_t* n_frames;    // [B]
+  int B, Tmax;
+  float* out;                 // [B][Tmax][n_mels]
+  const float* basis;         // [passes][33][C_hi,C_lo,S_hi,S_lo][2][nb][4]
+  const float2* melw;         // [nbt]
+  const uint32_t* meladv;     // [nbt/16], 2 bits per bin: filters that close before it
+  const float* norms;         // [n_mels] or null
+  const float* win;           // [512]: w[n] (n = 1..256) | w[512-n] (n = 1..255), 0
+  float wc;                   // w[512]
+  int passes, sp, nb, nbt, n_mels;
+  float clamp, power_eps;
+  int32_t* status;
+  float* dbg_reim;            // optional [total_frames][2*dbg_nbt], bins dbg_kmin..
+  int dbg_nbt, dbg_kmin, kmax;
+  int first_k[2];             // first live bin of each parity
+  int exp_flags;
+};
+
+struct __align__(8) Barriers {
+  uint64_t b_full[kBStages2], b_empty[kBStages2];
+  uint64_t a_full[kSets], a_empty[kSets];
+  uint64_t acc_full, acc_empty;
+};
+
+struct GroupInfo {
+  bool valid;
+  int b, t0, T;
+};
+
+__device__ __forceinline__ GroupInfo locate_group(const Params& P, int64_t G, int64_t total_groups) {
+  GroupInfo gi{false, 0, 0, 0};
+  if (G >= total_groups) return gi;
+  gi.valid = true;
+  if (P.T_uniform) {
+    gi.b = (int)(G / P.G_uniform);
+    gi.t0 = (int)(G - (int64_t)gi.b * P.G_uniform) * kGroup;
+    gi.T = P.T_uniform;
+  } else {
+    gi.b = find_clip(P.group_off, P.B, G);
+    gi.t0 = (int)(G - P.group_off[gi.b]) * kGroup;
+    gi.T = P.n_frames[gi.b];
+  }
+  return gi;
+}
+
+// Offset (in floats, relative to P.edge when *edge else P.src) of padded sample 256*tv + woff of clip b.
+__device__ __forceinline__ int32_t sample_offset(const Params& P, int b, int T, int tv, int woff, bool* edge) {
+  *edge = false;
+  if (!P.direct) return (int32_t)((int64_t)b * P.src_stride + (int64_t)kHop * tv + woff);
+  if (T <= 8 || tv < 8) { *edge = true; return b * kEdgeClip + kHop * tv + woff; }
+  if (tv >= T - 4) { *edge = true; return b * kEdgeClip + kEdgeA + kHop * (tv - (T - 4)) + woff; }
+  return (int32_t)((int64_t)b * P.src_stride + (int64_t)kHop * tv - P.pad + woff);
+}
+
+}  // namespace f2
+
+template <bool kPower1, bool kDebug>
+__global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P) {
+  using namespace f2;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  // ---- carve shared memory
+  const int nb = P.nb;
+  const uint32_t b_stage_bytes = (uint32_t)nb * 128u;       // 4 arrays x 2 k-halves x nb rows x 16 B
+  uint8_t* s_b = smem;                                       // basis ring
+  uint8_t* s_raw = s_b + (size_t)kBStages2 * b_stage_bytes;   // raw audio ring
+  float2* s_melw = reinterpret_cast<float2*>(s_raw + (size_t)kConvWarps2 * kDepth * kStageBytes);
+  uint32_t* s_adv = reinterpret_cast<uint32_t*>(s_melw + P.nbt);
+  float* s_win = reinterpret_cast<float*>(s_adv + ((P.nbt / 16 + 3) & ~3));       // [512]
+  float* s_norm = s_win + 512;                                       // [kMaxMels] mel_norms (or 1)
+  float* s_park = s_norm + kMaxMels;                                 // [128][n_mels+1] raw mel sums of the tile
+  const int park_pitch = P.n_mels + 1;
+  Barriers* bars = reinterpret_cast<Barriers*>(s_park + ((kTileM * park_pitch + 1) & ~1));
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t total_groups = P.group_off[P.B];
+  const int num_tiles = (int)((total_groups + 3) / 4);
+
+  // ---- one-time setup
+  for (int i = threadIdx.x; i < P.nbt; i += kThreads2) s_melw[i] = P.melw[i];
+  for (int i = threadIdx.x; i < P.nbt / 16; i += kThreads2) s_adv[i] = P.meladv[i];
+  for (int i = threadIdx.x; i < 512; i += kThreads2) s_win[i] = P.win[i];
+  for (int i = threadIdx.x; i < P.n_mels; i += kThreads2) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kBStages2; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
+    for (int i = 0; i < kSets; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
+    mbar_init(smem_u32(&bars->acc_full), 1);
+    mbar_init(smem_u32(&bars->acc_empty), 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpTmem) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *s_tmem;
+
+  if (warp == kWarpTma) {
+    // ===== basis producer: one bulk copy per k-step stage =====
+    if (lane == 0 && !(P.exp_flags & 2)) {
+      uint32_t seq = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+        for (int ps = 0; ps < P.passes; ++ps)
+          for (int ks = 0; ks < kKS; ++ks, ++seq) {
+            const uint32_t st = seq % kBStages2, use = seq / kBStages2;
+            mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
+            const uint32_t full = smem_u32(&bars->b_full[st]);
+            mbar_expect_tx(full, b_stage_bytes);
+            bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
+                     P.basis + ((size_t)ps * kKS + ks) * (b_stage_bytes / 4), b_stage_bytes, full);
+          }
+    }
+    __syncwarp();
+  } else if (warp == kWarpMma) {
+    // ===== MMA issuer: warp-uniform waits, one elected lane issues =====
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nb >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);          // SBO = 128 B, descriptor version 1
+    const uint32_t desc_lo0 = (((uint32_t)nb * 16u) >> 4) << 16;  // LBO = nb*16 B between the two k-halves
+    const uint32_t arr16 = ((uint32_t)nb * 32u) >> 4;           // one operand array, in 16 B units
+    const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
+    const uint32_t d_re = tmem, d_im = tmem + kNBMax;
+    uint32_t kseq = 0, pseq = 0;
+    uint32_t as = 0, ause = 0;                                   // A stage = kseq % kSets, its use count
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        if (!(P.exp_flags & 4)) mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        for (int ks = 0; ks < kKS; ++ks, ++kseq) {
+          const uint32_t st = kseq % kBStages2, use = kseq / kBStages2;
+          if (!(P.exp_flags & 1)) mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+          if (!(P.exp_flags & 2)) mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+          tc_fence_after();
+          if (elect_one_sync()) {
+            const uint32_t a_base = tmem + kColA2 + as * 32;
+            const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
+            const uint64_t c_hi = ((uint64_t)desc_hi << 32) | lo;
+            const uint64_t c_lo = ((uint64_t)desc_hi << 32) | (lo + arr16);
+            const uint64_t s_hi = ((uint64_t)desc_hi << 32) | (lo + 2 * arr16);
+            const uint64_t s_lo = ((uint64_t)desc_hi << 32) | (lo + 3 * arr16);
+            const uint32_t e_hi = a_base, e_lo = a_base + 8, o_hi = a_base + 16, o_lo = a_base + 24;
+            const uint32_t first = ks == 0 ? 0u : 1u;
+            if (!(P.exp_flags & 32)) {
+              mma_tf32_ts(d_re, e_lo, c_hi, idesc, first);   // small terms first
+              mma_tf32_ts(d_re, e_hi, c_lo, idesc, 1u);
+              mma_tf32_ts(d_re, e_hi, c_hi, idesc, 1u);
+              if (ks < kKS - 1) {                            // the centre-tap k-step has no sine part
+                mma_tf32_ts(d_im, o_lo, s_hi, idesc, first);
+                mma_tf32_ts(d_im, o_hi, s_lo, idesc, 1u);
+                mma_tf32_ts(d_im, o_hi, s_hi, idesc, 1u);
+              }
+            }
+            tc_commit(smem_u32(&bars->b_empty[st]));         // basis stage free once these MMAs retire
+            tc_commit(smem_u32(&bars->a_empty[as]));         // A stage free
+            if (ks == kKS - 1) tc_commit(smem_u32(&bars->acc_full));
+          }
+          __syncwarp();
+          if (++as == kSets) { as = 0; ++ause; }
+        }
+      }
+  }
+  else if (warp >= kWarpConv02 && warp < kWarpEpi02 && !(P.exp_flags & 1)) {
+    // ===== converters: stage own slots (cp.async) -> window + double fold + TF32 split -> TMEM A stage `set` =====
+    const int cw = warp - kWarpConv02;
+    const int set = cw >> 2;                           // A stage and k-step residue this warp serves
+    const int q = warp & 3;                            // TMEM lane quarter == group within the tile
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    uint8_t* my_raw = s_raw + (size_t)cw * kDepth * kStageBytes;
+
+    // piece table: piece idx = 32 i + lane of the stage = (slot sigma, 16 B piece 0..4 of the slot); pieces 0..2 are
+    // the forward window of frame sigma, pieces 3..4 the mirrored window of frame sigma - 2
+    uint32_t pc_dst[kPieceIters];                      // byte offset in the stage | piece << 16 | live << 31
+#pragma unroll
+    for (int i = 0; i < kPieceIters; ++i) {
+      const int idx = i * 32 + lane, sigma = idx / 5, piece = idx - sigma * 5;
+      pc_dst[i] = (uint32_t)(sigma * kSlotFloats * 4 + piece * 16) | ((uint32_t)piece << 16) | (idx < kPieces ? 0x80000000u : 0u);
+    }
+
+    struct Cursor { int tile, ps, ks; };
+    auto advance = [&](Cursor& c) -> bool {           // to this set's next k-step; true when it enters a new tile
+      c.ks += kSets;
+      if (c.ks >= kKS) {
+        c.ks -= kKS;
+        if (++c.ps >= P.passes) { c.ps = 0; c.tile += gridDim.x; return true; }
+      }
+      return false;
+    };
+
+    int32_t off[kPieceIters];
+    uint32_t okm = 0, edm = 0;
+    float xc_next = 0.f;                               // centre tap f[512] of this lane's row in the issue tile
+    auto load_tile = [&](int tile) {
+      okm = edm = 0;
+      xc_next = 0.f;
+      if (tile >= num_tiles) return;
+      const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
+      if (!gi.valid) return;
+#pragma unroll
+      for (int i = 0; i < kPieceIters; ++i) {
+        const int piece = (pc_dst[i] >> 16) & 7, sigma = (int)(pc_dst[i] & 0xffffu) / (kSlotFloats * 4);
+        const bool fwd = piece < 3;
+        const int tv = gi.t0 + (fwd ? sigma : sigma - 2);
+        const int woff = fwd ? 4 * piece : (kNfft - 8) + 4 * (piece - 3);
+        const bool ok = (pc_dst[i] >> 31) && (fwd ? tv <= gi.T + 1 : tv <= gi.T - 1);
+        bool edge;
+        off[i] = sample_offset(P, gi.b, gi.T, tv, woff, &edge);
+        okm |= (uint32_t)ok << i;
+        edm |= (uint32_t)(ok && edge) << i;
+      }
+      const int t = gi.t0 + lane;
+      if (t < gi.T) {
+        bool edge;
+        const int32_t o = sample_offset(P, gi.b, gi.T, t, kNfft / 2, &edge);
+        xc_next = __ldg((edge ? P.edge : P.src) + o);
+      }
+    };
+
+    Cursor ic{(int)blockIdx.x, 0, set};                // issue cursor, kDepth own k-steps ahead of the consume cursor
+    auto issue = [&](uint32_t stage) {
+      if (ic.tile < num_tiles && ic.ks < kKS - 1) {
+        const uint32_t base = smem_u32(my_raw + (size_t)stage * kStageBytes);
+        const int adv = kKStep * ic.ks;
+#pragma unroll
+        for (int i = 0; i < kPieceIters; ++i) {
+          if (pc_dst[i] >> 31) {
+            const bool ok = (okm >> i) & 1u;
+            const bool fwd = ((pc_dst[i] >> 16) & 7) < 3;
+            const float* bp = ((edm >> i) & 1u) ? P.edge : P.src;
+            cp_async16(base + (pc_dst[i] & 0xffffu), ok ? bp + (off[i] + (fwd ? adv : -adv)) : P.src, ok ? 16u : 0u);
+          }
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");   // empty groups keep the wait_group count uniform
+      if (ic.tile < num_tiles && advance(ic)) load_tile(ic.tile);
+    };
+
+    load_tile(ic.tile);
+    float xc = xc_next;
+#pragma unroll
+    for (int d = 0; d < kDepth; ++d) issue(d);
+
+    Cursor cc{(int)blockIdx.x, 0, set};
+    uint32_t mine = 0;
+    const uint32_t a_base = tmem + lane_addr + kColA2 + set * 32;
+    while (cc.tile < num_tiles) {
+      const uint32_t stage = mine % kDepth;
+      asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
+      __syncwarp();
+      uint32_t ehi[8], elo[8], ohi[8], olo[8];
+      const bool centre = cc.ks == kKS - 1;
+      if (!centre) {
+        const float4* s0 = reinterpret_cast<const float4*>(my_raw + (size_t)stage * kStageBytes) + lane * 5;
+        const float4* s2 = s0 + 10;                    // slot lane + 2
+        float a[12], c[8], d[12], b[8];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const float4 v = s0[i], u = s2[i];
+          a[4 * i] = v.x; a[4 * i + 1] = v.y; a[4 * i + 2] = v.z; a[4 * i + 3] = v.w;
+          d[4 * i] = u.x; d[4 * i + 1] = u.y; d[4 * i + 2] = u.z; d[4 * i + 3] = u.w;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const float4 v = s0[3 + i], u = s2[3 + i];
+          c[4 * i] = v.x; c[4 * i + 1] = v.y; c[4 * i + 2] = v.z; c[4 * i + 3] = v.w;
+          b[4 * i] = u.x; b[4 * i + 1] = u.y; b[4 * i + 2] = u.z; b[4 * i + 3] = u.w;
+        }
+        float w1[8], w2[8];
+        {
+          const float4* wp = reinterpret_cast<const float4*>(s_win + kKStep * cc.ks);
+          const float4 p0 = wp[0], p1 = wp[1], r0 = wp[64], r1 = wp[65];
+          w1[0] = p0.x; w1[1] = p0.y; w1[2] = p0.z; w1[3] = p0.w; w1[4] = p1.x; w1[5] = p1.y; w1[6] = p1.z; w1[7] = p1.w;
+          w2[0] = r0.x; w2[1] = r0.y; w2[2] = r0.z; w2[3] = r0.w; w2[4] = r1.x; w2[5] = r1.y; w2[6] = r1.z; w2[7] = r1.w;
+        }
+        const float sgn = (cc.ps >= P.sp) ? -1.f : 1.f;   // passes [0, sp) are the even bins, [sp, 2 sp) the odd bins
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float fa = a[1 + j], fb = b[7 - j], fc = c[7 - j], fd = d[1 + j];   // f[n], f[N-n], f[512-n], f[512+n]
+          const float w2s = sgn * w2[j];
+          const float e = fmaf(w2s, fc + fd, w1[j] * (fa + fb));
+          const float o = fmaf(-w2s, fc - fd, w1[j] * (fa - fb));
+          const uint32_t he = __float_as_uint(e) & 0xFFFFE000u, ho = __float_as_uint(o) & 0xFFFFE000u;
+          ehi[j] = he; elo[j] = __float_as_uint(e - __uint_as_float(he));
+          ohi[j] = ho; olo[j] = __float_as_uint(o - __uint_as_float(ho));
+        }
+      } else {
+        const float e = P.wc * xc;
+        const uint32_t he = __float_as_uint(e) & 0xFFFFE000u;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { ehi[j] = 0u; elo[j] = 0u; ohi[j] = 0u; olo[j] = 0u; }
+        ehi[0] = he; elo[0] = __float_as_uint(e - __uint_as_float(he));
+      }
+      __syncwarp();                                    // every lane has its taps in registers: the stage can be refilled
+      issue(stage);
+      mbar_wait(smem_u32(&bars->a_empty[set]), (mine & 1) ^ 1, P.status, 402);
+      tc_fence_after();
+      tmem_st8(a_base + 0, ehi);
+      tmem_st8(a_base + 8, elo);
+      if (!centre) {
+        tmem_st8(a_base + 16, ohi);
+        tmem_st8(a_base + 24, olo);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[set]));
+      ++mine;
+      if (advance(cc)) xc = xc_next;
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  }
+  else if (warp >= kWarpEpi02 && !(P.exp_flags & 4)) {
+    // ===== epilogue: power -> sparse mel (per parity) -> log(clamp) -> / norm =====
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    const uint32_t t_re = tmem + lane_addr, t_im = t_re + kNBMax;
+    float* const pp0 = s_park + r * park_pitch;
+    float* const pp_end = pp0 + P.n_mels;
+    const int nblk = nb >> 4;
+    uint32_t pseq = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
+      const int t = gi.t0 + lane;
+      const bool valid = gi.valid && t < gi.T && t < P.Tmax;
+      float* orow = valid ? P.out + ((int64_t)gi.b * P.Tmax + t) * P.n_mels : nullptr;
+      int64_t gdbg = -1;
+      if (kDebug) { if (valid) gdbg = P.frame_off[gi.b] + t; }
+      // Running pair of adjacent filters (cur, cur+1) over the bins of ONE parity in ascending order; the host table
+      // says how many filters close before each bin.  The first parity stores its raw sums, the second adds to them.
+      float run_lo = 0.f, run_hi = 0.f;
+      float* pp = pp0;
+      bool add = false;
+      auto park = [&]() {
+        float v = run_lo;
+        if (add) v += *pp;
+        *pp++ = v;
+        run_lo = run_hi; run_hi = 0.f;
+      };
+      auto drain16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0) {
+        const uint32_t advw = s_adv[bin0 >> 4];
+        const float4* wp = reinterpret_cast<const float4*>(s_melw + bin0);
+#pragma unroll
+        for (int j2 = 0; j2 < 8; ++j2) {
+          const float4 w2 = wp[j2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int j = 2 * j2 + h;
+            const uint32_t cnt = (advw >> (2 * j)) & 3u;    // warp-uniform
+            if (cnt) { park(); if (cnt > 1) { park(); if (cnt > 2) park(); } }
+            const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
+            float pw = fmaf(a, a, bq * bq);
+            if (kPower1) pw = sqrtf(pw + P.power_eps);
+            run_lo = fmaf(h ? w2.z : w2.x, pw, run_lo);
+            run_hi = fmaf(h ? w2.w : w2.y, pw, run_hi);
+          }
+        }
+      };
+      auto dump16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int ps, int blk) {
+        if (kDebug) {
+          if (gdbg >= 0) {
+            const int par = ps / P.sp, sub = ps - par * P.sp;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int k = P.first_k[par] + 2 * (sub * nb + blk * 16 + j);
+              if (k <= P.kmax) {
+                float* d = P.dbg_reim + gdbg * (2 * P.dbg_nbt) + (k - P.dbg_kmin);
+                d[0] = __uint_as_float(re[j]);
+                d[P.dbg_nbt] = __uint_as_float(im[j]);
+              }
+            }
+          }
+        }
+      };
+      auto release_acc = [&]() {        // accumulators of this pass are in registers: hand TMEM back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
+      };
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        if (ps == P.sp) {               // second parity: close the first one, restart the scan, accumulate
+          while (pp < pp_end) park();
+          pp = pp0; run_lo = run_hi = 0.f; add = true;
+        }
+        mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
+        tc_fence_after();
+        uint32_t reA[16], imA[16], reB[16], imB[16];
+        tmem_ld16(t_re, reA);
+        tmem_ld16(t_im, imA);
+        for (int blk = 0; blk < nblk; blk += 2) {
+          tmem_wait_ld();                                          // set A = block blk
+          if (blk + 1 < nblk) {
+            tmem_ld16(t_re + (blk + 1) * 16, reB);
+            tmem_ld16(t_im + (blk + 1) * 16, imB);
+          } else {
+            release_acc();
+          }
+          dump16(reA, imA, ps, blk);
+          if (!(P.exp_flags & 8)) drain16(reA, imA, ps * nb + blk * 16);
+          if (blk + 1 < nblk) {
+            tmem_wait_ld();                                        // set B = block blk+1
+            if (blk + 2 < nblk) {
+              tmem_ld16(t_re + (blk + 2) * 16, reA);
+              tmem_ld16(t_im + (blk + 2) * 16, imA);
+            } else {
+              release_acc();
+            }
+            dump16(reB, imB, ps, blk + 1);
+            if (!(P.exp_flags & 8)) drain16(reB, imB, ps * nb + (blk + 1) * 16);
+          }
+        }
+      }
+      while (pp < pp_end) park();       // close the running filters (and add nothing to the ones above them)
+      // raw mel sums -> log(max(., clamp)) / norm, one coalesced output row at a time
+      __syncwarp();
+#pragma unroll 4
+      for (int rr = 0; rr < ((P.exp_flags & 16) ? 0 : 32); ++rr) {
+        const unsigned long long pr = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr);
+        if (!pr) continue;
+        float* rowp = reinterpret_cast<float*>((uintptr_t)pr);
+        const float* parked = s_park + (q * 32 + rr) * park_pitch;
+        for (int mth = lane; mth < P.n_mels; mth += 32)
+          rowp[mth] = logf(fmaxf(parked[mth], P.clamp)) / s_norm[mth];   // true division, as the reference
+      }
+      __syncwarp();
+    }
+  }
+
+  // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWarpTmem) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTmemCols) : "memory");
+  }
+}

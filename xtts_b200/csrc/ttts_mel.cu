@@ -115,6 +115,18 @@ struct ttts_mel_plan {
   float* d_cosf = nullptr;     // [512][nbt] plain fp32 folded basis for k_simt
   float* d_sinf = nullptr;
   float* d_fb = nullptr;       // [nbt][n_mels] dense filterbank rows of the live bins for k_simt
+  // double-fold kernel (k_logmel2.cuh): even / odd bins are separate passes over K = 256 (+ centre tap)
+  int algo = 2;        // 2 = k_logmel2 (default), 1 = k_logmel (TTTS_MEL_ALGO=1)
+  int kmax = 0;
+  int first_k[2] = {0, 0};   // first live bin of each parity
+  int sp = 0;          // passes per parity
+  int nb2 = 0;         // bins per pass
+  int nbt2 = 0;        // 2 * sp * nb2
+  float wc = 0.f;      // centre tap weight w[512] * spec_scale
+  float* d_basis2 = nullptr;   // [2 sp][33 k-steps][4 arrays][2 k-halves][nb2][4] fp32 (TF32-exact values), no window
+  float2* d_melw2 = nullptr;   // [nbt2]
+  uint32_t* d_meladv2 = nullptr;  // [nbt2/16], 2 bits per bin
+  float* d_win2 = nullptr;     // [512]
 };
 
 // ------------------------------------------------------------------------------------------
@@ -245,6 +257,79 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
             }
     }
 
+  // ---- double-fold tables (k_logmel2.cuh)
+  p->kmax = kmax;
+  p->first_k[kmin & 1] = kmin;
+  p->first_k[(kmin & 1) ^ 1] = kmin + 1;
+  int n_par[2];
+  for (int q = 0; q < 2; ++q) n_par[q] = p->first_k[q] <= kmax ? (kmax - p->first_k[q]) / 2 + 1 : 0;
+  const int n_par_max = n_par[0] > n_par[1] ? n_par[0] : n_par[1];
+  p->sp = (n_par_max + kNBMax - 1) / kNBMax;
+  p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 16);
+  p->nbt2 = 2 * p->sp * p->nb2;
+  if (const char* e2 = getenv("TTTS_MEL_ALGO")) p->algo = atoi(e2) == 1 ? 1 : 2;
+  const int nb2 = p->nb2, nbt2 = p->nbt2, per_par = p->sp * p->nb2;
+  std::vector<float2> melw2(nbt2, make_float2(0.f, 0.f));
+  std::vector<uint32_t> meladv2(nbt2 / 16, 0u);
+  for (int par = 0; par < 2; ++par) {
+    int cur2 = 0;
+    for (int idx = 0; idx < per_par; ++idx) {
+      const int k = p->first_k[par] + 2 * idx, j = par * per_par + idx;
+      if (k > kmax) break;
+      const float* row = fb + (size_t)k * nm;
+      int first = -1, last = -1;
+      for (int m = 0; m < nm; ++m)
+        if (row[m] != 0.f) { if (first < 0) first = m; last = m; }
+      if (first < 0) continue;
+      if (last - first > 1 || first < cur2 || first - cur2 > 3) {
+        delete p;
+        return fail(TTTS_MEL_EINVAL, "filterbank row %d: need <= two adjacent, non-decreasing filters per bin", k);
+      }
+      meladv2[j >> 4] |= (uint32_t)(first - cur2) << (2 * (j & 15));
+      cur2 = first;
+      melw2[j] = make_float2(row[first], last > first ? row[last] : 0.f);
+    }
+  }
+  std::vector<float> win2(512, 0.f);
+  for (int n = 1; n <= 256; ++n) {
+    win2[n - 1] = (float)(0.5 * ((double)window[n] + (double)window[N - n]) * scale);
+    if (n < 256) win2[256 + n - 1] = (float)(0.5 * ((double)window[512 - n] + (double)window[512 + n]) * scale);
+  }
+  p->wc = (float)((double)window[N / 2] * scale);
+  const size_t stage2_floats = (size_t)4 * 2 * nb2 * 4;
+  std::vector<float> img2((size_t)2 * p->sp * 33 * stage2_floats, 0.f);
+  {
+    static const double kQuarter[4] = {1.0, 0.0, -1.0, 0.0};
+    for (int ps = 0; ps < 2 * p->sp; ++ps) {
+      const int par = ps / p->sp, sub = ps % p->sp;
+      for (int ks = 0; ks < 33; ++ks) {
+        float* st = img2.data() + ((size_t)ps * 33 + ks) * stage2_floats;
+        for (int j = 0; j < 2; ++j)
+          for (int r = 0; r < nb2; ++r) {
+            const int k = p->first_k[par] + 2 * (sub * nb2 + r);
+            if (k > kmax) continue;
+            for (int e4 = 0; e4 < 4; ++e4) {
+              double c, sn;
+              if (ks < 32) {
+                const int n = ks * kKStep + j * 4 + e4 + 1;
+                const int rr = (int)(((long long)k * n) % N);
+                if (rr % (N / 4) == 0) { c = kQuarter[rr / (N / 4)]; sn = kQuarter[(rr / (N / 4) + 3) & 3]; }
+                else { const double ang = 2.0 * M_PI * (double)rr / (double)N; c = cos(ang); sn = sin(ang); }
+              } else {                       // centre tap n = 512: cos(pi k) = (-1)^k, sin = 0; one live slot
+                c = (j == 0 && e4 == 0) ? ((k & 1) ? -1.0 : 1.0) : 0.0;
+                sn = 0.0;
+              }
+              for (int arr = 0; arr < 4; ++arr) {
+                const double v = arr < 2 ? c : sn;
+                const float hi = tf32_rn(v);
+                st[(((size_t)arr * 2 + j) * nb2 + r) * 4 + e4] = (arr & 1) ? tf32_rn(v - (double)hi) : hi;
+              }
+            }
+          }
+      }
+    }
+  }
+
   cudaError_t e;
   int dev = 0;
   e = cudaGetDevice(&dev);
@@ -261,6 +346,10 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   up((void**)&p->d_cosf, cosf.data(), cosf.size() * 4);
   up((void**)&p->d_sinf, sinf_.data(), sinf_.size() * 4);
   up((void**)&p->d_fb, fbl.data(), fbl.size() * 4);
+  up((void**)&p->d_basis2, img2.data(), img2.size() * 4);
+  up((void**)&p->d_melw2, melw2.data(), melw2.size() * sizeof(float2));
+  up((void**)&p->d_meladv2, meladv2.data(), meladv2.size() * sizeof(uint32_t));
+  up((void**)&p->d_win2, win2.data(), win2.size() * 4);
   if (e != cudaSuccess) {
     int rc = fail(TTTS_MEL_ECUDA, "plan upload: %s", cudaGetErrorString(e));
     ttts_mel_plan_destroy(p);
@@ -286,6 +375,7 @@ extern "C" void ttts_mel_plan_destroy(ttts_mel_plan* p) {
   if (!p) return;
   cudaFree(p->d_basis); cudaFree(p->d_melw); cudaFree(p->d_meladv); cudaFree(p->d_norms);
   cudaFree(p->d_cosf); cudaFree(p->d_sinf); cudaFree(p->d_fb);
+  cudaFree(p->d_basis2); cudaFree(p->d_melw2); cudaFree(p->d_meladv2); cudaFree(p->d_win2);
   delete p;
 }
 
@@ -311,6 +401,7 @@ namespace {
 struct Workspace {
   int32_t* status;      // [64] word 0 = device error code
   int64_t* frame_off;   // [B+1]
+  int64_t* group_off;   // [B+1] exclusive prefix of ceil(n_frames / 32) (k_logmel2's row layout)
   int32_t* n_frames;    // [B]
   float* xp;            // [B][Lp]   (k_simt and unaligned inputs only)
   float* edge;          // [B][kEdgeClip] reflect-padded samples of each clip's first and last frames
@@ -326,6 +417,7 @@ Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
   char* b = (char*)base;
   w.status = (int32_t*)(b + off); off += 256;
   w.frame_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
+  w.group_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.n_frames = (int32_t*)(b + off); off += align_up((size_t)B * 4, 256);
   w.edge = (float*)(b + off); off += align_up((size_t)B * kEdgeClip * 4, 256);
   w.xp = (float*)(b + off); off += align_up((size_t)B * (size_t)w.Lp * 4, 256);
@@ -460,7 +552,7 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
                                                const int64_t* __restrict__ lengths, int B, int64_t Lmax, int pad,
                                                int Tmax, int32_t* __restrict__ n_frames,
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
-                                               int32_t* __restrict__ status) {
+                                               int64_t* __restrict__ group_off, int32_t* __restrict__ status) {
   if (blockIdx.x > 0) { clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, blockIdx.x - 1); return; }
   __shared__ long long part[1024];
   const int tid = threadIdx.x;
@@ -489,6 +581,21 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
   long long run = part[tid] - sum;
   for (int b = b0; b < b1; ++b) { frame_off[b] = run; run += n_frames[b]; }
   if (tid == 1023) frame_off[B] = part[1023];
+  // second prefix: groups of 32 frames per clip
+  __syncthreads();
+  long long gsum = 0;
+  for (int b = b0; b < b1; ++b) gsum += (n_frames[b] + 31) >> 5;
+  part[tid] = gsum;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const long long v = tid >= d ? part[tid - d] : 0;
+    __syncthreads();
+    part[tid] += v;
+    __syncthreads();
+  }
+  run = part[tid] - gsum;
+  for (int b = b0; b < b1; ++b) { group_off[b] = run; run += (n_frames[b] + 31) >> 5; }
+  if (tid == 1023) group_off[B] = part[1023];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -591,7 +698,7 @@ struct LogmelParams {
   int power_is_1;
   int32_t* status;
   float* dbg_reim;            // optional [total_frames][2*nbt]
-  int exp_flags;              // timing experiments (results invalid): 1 no A handoff, 2 no basis loads, 4 no epilogue
+  int exp_flags;              // timing experiments (results invalid): 1 no A handoff, 2 no basis loads, 4 no epilogue, 32 no MMAs (commits only)
 };
 
 struct __align__(8) LogmelBarriers {
@@ -689,12 +796,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
               const uint64_t s_lo = ((uint64_t)desc_hi << 32) | (lo + 3 * arr16);
               const uint32_t e_hi = a_base, e_lo = a_base + 8, o_hi = a_base + 16, o_lo = a_base + 24;
               const uint32_t first = (c == 0 && kk == 0) ? 0u : 1u;
+              if (!(P.exp_flags & 32)) {
               mma_tf32_ts(d_re, e_lo, c_hi, idesc, first);   // small terms first
               mma_tf32_ts(d_re, e_hi, c_lo, idesc, 1u);
               mma_tf32_ts(d_re, e_hi, c_hi, idesc, 1u);
               mma_tf32_ts(d_im, o_lo, s_hi, idesc, first);
               mma_tf32_ts(d_im, o_hi, s_lo, idesc, 1u);
               mma_tf32_ts(d_im, o_hi, s_hi, idesc, 1u);
+              }
               tc_commit(smem_u32(&bars->b_empty[st]));       // basis stage free once these MMAs retire
               tc_commit(smem_u32(&bars->a_empty[as]));       // A stage free
               if (c == kChunks - 1 && kk == kKC / kKStep - 1)
@@ -953,6 +1062,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
   }
 }
 
+#include "k_logmel2.cuh"
+
 // ------------------------------------------------------------------------------------------
 // k_simt: plain CUDA-core fp32 implementation of the same maths (cross-check kernel)
 // ------------------------------------------------------------------------------------------
@@ -1073,6 +1184,13 @@ size_t logmel_smem_bytes(const ttts_mel_plan* p) {
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
 }
 
+size_t logmel2_smem_bytes(const ttts_mel_plan* p) {
+  size_t s = (size_t)f2::kBStages2 * p->nb2 * 128 + (size_t)f2::kConvWarps2 * f2::kDepth * f2::kStageBytes +
+             (size_t)p->nbt2 * sizeof(float2) + (size_t)(p->nbt2 / 16 + 4) * 4 + 512 * 4 + kMaxMels * 4 +
+             (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + sizeof(f2::Barriers) + 16;
+  return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
+}
+
 enum class Impl { Tcgen05, Simt };
 
 int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, const int64_t* lengths, int32_t B,
@@ -1094,7 +1212,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   // into the workspace first.
   const bool direct = impl == Impl::Tcgen05 && vec_ok && (int64_t)B * row_stride < ((int64_t)1 << 31);
   k_prep<<<B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
-                                     p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.status);
+                                     p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status);
   ++g_launches;
   if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
@@ -1102,7 +1220,35 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     k_pad<<<grid, 256, 0, stream>>>(wav, row_stride, lengths, Lmax, p->cfg.pad, w.xp, w.Lp, vec_ok);
     ++g_launches;
   }
-  if (impl == Impl::Tcgen05) {
+  if (impl == Impl::Tcgen05 && p->algo == 2) {
+    f2::Params P{};
+    P.src = direct ? wav : w.xp; P.src_stride = direct ? row_stride : w.Lp; P.edge = w.edge;
+    P.lengths = lengths; P.Lmax = Lmax; P.direct = direct; P.pad = p->cfg.pad;
+    {
+      const int64_t Tu = ttts_mel_frames(p, Lmax);
+      P.T_uniform = lengths ? 0 : (int)(Tu < Tmax ? Tu : Tmax);
+      P.G_uniform = (P.T_uniform + f2::kGroup - 1) / f2::kGroup;
+    }
+    P.group_off = w.group_off; P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
+    P.out = out; P.basis = p->d_basis2; P.melw = p->d_melw2; P.meladv = p->d_meladv2; P.norms = p->d_norms;
+    P.win = p->d_win2; P.wc = p->wc;
+    P.passes = 2 * p->sp; P.sp = p->sp; P.nb = p->nb2; P.nbt = p->nbt2; P.n_mels = p->cfg.n_mels;
+    P.clamp = p->cfg.clamp; P.power_eps = p->cfg.power_eps; P.status = w.status;
+    P.dbg_reim = dbg_reim; P.dbg_nbt = p->nbt; P.dbg_kmin = p->kmin; P.kmax = p->kmax;
+    P.first_k[0] = p->first_k[0]; P.first_k[1] = p->first_k[1];
+    P.exp_flags = g_exp_flags;
+    const size_t smem = logmel2_smem_bytes(p);
+    const bool pw1 = p->cfg.power == 1.0f;
+    void (*kern)(const f2::Params) =
+        dbg_reim ? (pw1 ? k_logmel2<true, true> : k_logmel2<false, true>)
+                 : (pw1 ? k_logmel2<true, false> : k_logmel2<false, false>);
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
+    if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
+    kern<<<p->num_sms, f2::kThreads2, smem, stream>>>(P);
+    if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
+    ++g_launches;
+  } else if (impl == Impl::Tcgen05) {
     LogmelParams P{};
     P.src = direct ? wav : w.xp; P.src_stride = direct ? row_stride : w.Lp; P.edge = w.edge;
     P.lengths = lengths; P.Lmax = Lmax; P.direct = direct; P.pad = p->cfg.pad;
