@@ -57,7 +57,7 @@ struct Params {
   float* out;                 // [B][Tmax][n_mels]
   const float* basis;         // [passes][33][C_hi,C_lo,S_hi,S_lo][2][nb][4]
   const float2* melw;         // [nbt]
-  const uint32_t* meladv;     // [nbt/16], 2 bits per bin: filters that close before it
+  const uint32_t* meladv;     // [2][nbt/16]: (bit j: one filter closes before bin j | bit 16+j: 2..3 close), 2-bit counts
   const float* norms;         // [n_mels] or null
   const float* win;           // [512]: w[n] (n = 1..256) | w[512-n] (n = 1..255), 0
   float wc;                   // w[512]
@@ -106,6 +106,23 @@ __device__ __forceinline__ int32_t sample_offset(const Params& P, int b, int T, 
   return (int32_t)((int64_t)b * P.src_stride + (int64_t)kHop * tv - P.pad + woff);
 }
 
+__device__ __forceinline__ void st_s(uint32_t addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+__device__ __forceinline__ float ld_s(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+// Rare event of the mel scan: `cnt` = 2 or 3 filters close before the next bin (narrow low-frequency filters).  Stores
+// the running pair and re-primes (run_lo, run_hi, next) from the parked sums of the filters that become active.
+// Out of line on purpose: the accumulator drain stays short; the common single close is predicated inline.
+__device__ __noinline__ float4 park_multi(uint32_t pa, float lo, float hi, float nx, uint32_t cnt) {
+  st_s(pa, lo);
+  st_s(pa + 4, hi);
+  if (cnt == 2) return make_float4(nx, ld_s(pa + 12), ld_s(pa + 16), 0.f);
+  return make_float4(ld_s(pa + 12), ld_s(pa + 16), ld_s(pa + 20), 0.f);
+}
+
 }  // namespace f2
 
 template <bool kPower1, bool kDebug>
@@ -118,8 +135,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   uint8_t* s_b = smem;                                       // basis ring
   uint8_t* s_raw = s_b + (size_t)kBStages2 * b_stage_bytes;   // raw audio ring
   float2* s_melw = reinterpret_cast<float2*>(s_raw + (size_t)kConvWarps2 * kDepth * kStageBytes);
-  uint32_t* s_adv = reinterpret_cast<uint32_t*>(s_melw + P.nbt);
-  float* s_win = reinterpret_cast<float*>(s_adv + ((P.nbt / 16 + 3) & ~3));       // [512]
+  uint32_t* s_adv = reinterpret_cast<uint32_t*>(s_melw + P.nbt);                  // [nbt/16] single / multi close masks
+  uint32_t* s_adv2 = s_adv + P.nbt / 16;                                           // [nbt/16] 2-bit close counts
+  float* s_win = reinterpret_cast<float*>(s_adv + ((2 * (P.nbt / 16) + 3) & ~3));  // [512]
   float* s_norm = s_win + 512;                                       // [kMaxMels] mel_norms (or 1)
   float* s_park = s_norm + kMaxMels;                                 // [128][n_mels+1] raw mel sums of the tile
   const int park_pitch = P.n_mels + 1;
@@ -132,9 +150,10 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 
   // ---- one-time setup
   for (int i = threadIdx.x; i < P.nbt; i += kThreads2) s_melw[i] = P.melw[i];
-  for (int i = threadIdx.x; i < P.nbt / 16; i += kThreads2) s_adv[i] = P.meladv[i];
+  for (int i = threadIdx.x; i < 2 * (P.nbt / 16); i += kThreads2) s_adv[i] = P.meladv[i];
   for (int i = threadIdx.x; i < 512; i += kThreads2) s_win[i] = P.win[i];
   for (int i = threadIdx.x; i < P.n_mels; i += kThreads2) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
+  for (int i = threadIdx.x; i < kTileM * park_pitch; i += kThreads2) s_park[i] = 0.f;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStages2; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
     for (int i = 0; i < kSets; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
@@ -368,9 +387,13 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const uint32_t t_re = tmem + lane_addr, t_im = t_re + kNBMax;
-    float* const pp0 = s_park + r * park_pitch;
-    float* const pp_end = pp0 + P.n_mels;
     const int nblk = nb >> 4;
+    float nrm[4], rnrm[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      nrm[k] = (lane + 32 * k < P.n_mels) ? s_norm[lane + 32 * k] : 1.f;
+      rnrm[k] = 1.0f / nrm[k];
+    }
     uint32_t pseq = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
@@ -379,19 +402,14 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       float* orow = valid ? P.out + ((int64_t)gi.b * P.Tmax + t) * P.n_mels : nullptr;
       int64_t gdbg = -1;
       if (kDebug) { if (valid) gdbg = P.frame_off[gi.b] + t; }
-      // Running pair of adjacent filters (cur, cur+1) over the bins of ONE parity in ascending order; the host table
-      // says how many filters close before each bin.  The first parity stores its raw sums, the second adds to them.
-      float run_lo = 0.f, run_hi = 0.f;
-      float* pp = pp0;
-      bool add = false;
-      auto park = [&]() {
-        float v = run_lo;
-        if (add) v += *pp;
-        *pp++ = v;
-        run_lo = run_hi; run_hi = 0.f;
-      };
-      auto drain16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0) {
-        const uint32_t advw = s_adv[bin0 >> 4];
+      // Running pair of adjacent filters (cur, cur+1) over the bins of ONE parity in ascending order.  The pair (and `nx`,
+      // the filter that becomes active next) is primed from the parked sums, so the second parity continues the first
+      // one's sums and every close is a plain store.  Host table: bit j = one filter closes before bin j (predicated
+      // inline), bit 16+j = two or three close (rare, out of line, count in the 2-bit table).
+      const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
+      uint32_t pa = pa0;
+      float run_lo = 0.f, run_hi = 0.f, nx = 0.f;      // parked sums are zero at the start of a tile
+      auto drain16x = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0, const uint32_t advw, auto multi) {
         const float4* wp = reinterpret_cast<const float4*>(s_melw + bin0);
 #pragma unroll
         for (int j2 = 0; j2 < 8; ++j2) {
@@ -399,8 +417,18 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             const int j = 2 * j2 + h;
-            const uint32_t cnt = (advw >> (2 * j)) & 3u;    // warp-uniform
-            if (cnt) { park(); if (cnt > 1) { park(); if (cnt > 2) park(); } }
+            if (decltype(multi)::value && (advw & (0x10000u << j))) {   // warp-uniform, rare
+              const uint32_t cnt = (s_adv2[bin0 >> 4] >> (2 * j)) & 3u;
+              const float4 t4 = park_multi(pa, run_lo, run_hi, nx, cnt);
+              run_lo = t4.x; run_hi = t4.y; nx = t4.z;
+              pa += 4 * cnt;
+            }
+            if (advw & (1u << j)) {                      // warp-uniform: one filter closes before this bin
+              st_s(pa, run_lo);
+              run_lo = run_hi; run_hi = nx;
+              nx = ld_s(pa + 12);
+              pa += 4;
+            }
             const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
             float pw = fmaf(a, a, bq * bq);
             if (kPower1) pw = sqrtf(pw + P.power_eps);
@@ -408,6 +436,12 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             run_hi = fmaf(h ? w2.w : w2.y, pw, run_hi);
           }
         }
+      };
+      // blocks without a multi-close (all but the lowest one or two of a parity) run the branch-free variant
+      auto drain16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0) {
+        const uint32_t advw = s_adv[bin0 >> 4];
+        if (advw >> 16) drain16x(re, im, bin0, advw, std::true_type{});
+        else drain16x(re, im, bin0, advw, std::false_type{});
       };
       auto dump16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int ps, int blk) {
         if (kDebug) {
@@ -431,9 +465,10 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
       };
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        if (ps == P.sp) {               // second parity: close the first one, restart the scan, accumulate
-          while (pp < pp_end) park();
-          pp = pp0; run_lo = run_hi = 0.f; add = true;
+        if (ps == P.sp) {               // second parity: close the first one, restart the scan on top of its sums
+          st_s(pa, run_lo); st_s(pa + 4, run_hi);
+          pa = pa0;
+          run_lo = ld_s(pa); run_hi = ld_s(pa + 4); nx = ld_s(pa + 8);
         }
         mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
         tc_fence_after();
@@ -463,17 +498,41 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           }
         }
       }
-      while (pp < pp_end) park();       // close the running filters (and add nothing to the ones above them)
-      // raw mel sums -> log(max(., clamp)) / norm, one coalesced output row at a time
+      st_s(pa, run_lo); st_s(pa + 4, run_hi);   // close the running pair
+      // raw mel sums -> log(max(., clamp)) / norm: coalesced output rows, 4 rows x up to 4 columns per lane in flight
+      // (independent logf / division chains), and the park rows are handed back zeroed for the next tile
       __syncwarp();
-#pragma unroll 4
-      for (int rr = 0; rr < ((P.exp_flags & 16) ? 0 : 32); ++rr) {
-        const unsigned long long pr = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr);
-        if (!pr) continue;
-        float* rowp = reinterpret_cast<float*>((uintptr_t)pr);
-        const float* parked = s_park + (q * 32 + rr) * park_pitch;
-        for (int mth = lane; mth < P.n_mels; mth += 32)
-          rowp[mth] = logf(fmaxf(parked[mth], P.clamp)) / s_norm[mth];   // true division, as the reference
+      for (int rr0 = 0; rr0 < ((P.exp_flags & 16) ? 0 : 32); rr0 += 4) {
+        float* rowp[4];
+        float v[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          rowp[i] = reinterpret_cast<float*>((uintptr_t)__shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr0 + i));
+          float* parked = s_park + (q * 32 + rr0 + i) * park_pitch + lane;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            v[i][k] = 1.f;
+            if (lane + 32 * k < P.n_mels) { v[i][k] = parked[32 * k]; parked[32 * k] = 0.f; }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (32 * k < P.n_mels) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              // x / norm as reciprocal + one Newton correction: branch-free (the IEEE division's slow-path call would
+              // serialise the independent chains) and equal to the correctly rounded quotient except in rare last-bit ties
+              const float x = logf(fmaxf(v[i][k], P.clamp));
+              const float y = x * rnrm[k];
+              v[i][k] = fabsf(y) < 3.0e38f ? fmaf(fmaf(-y, nrm[k], x), rnrm[k], y) : y;   // norm 0 / inf: keep x * (1/norm)
+            }
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (rowp[i] && lane + 32 * k < P.n_mels) rowp[i][lane + 32 * k] = v[i][k];
       }
       __syncwarp();
     }

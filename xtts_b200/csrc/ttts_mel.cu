@@ -30,6 +30,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 #include <vector>
 
 // ------------------------------------------------------------------------------------------
@@ -270,7 +271,7 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   if (const char* e2 = getenv("TTTS_MEL_ALGO")) p->algo = atoi(e2) == 1 ? 1 : 2;
   const int nb2 = p->nb2, nbt2 = p->nbt2, per_par = p->sp * p->nb2;
   std::vector<float2> melw2(nbt2, make_float2(0.f, 0.f));
-  std::vector<uint32_t> meladv2(nbt2 / 16, 0u);
+  std::vector<uint32_t> meladv2(2 * (nbt2 / 16), 0u);   // [0]: single / multi close masks, [1]: 2-bit counts
   for (int par = 0; par < 2; ++par) {
     int cur2 = 0;
     for (int idx = 0; idx < per_par; ++idx) {
@@ -285,7 +286,10 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
         delete p;
         return fail(TTTS_MEL_EINVAL, "filterbank row %d: need <= two adjacent, non-decreasing filters per bin", k);
       }
-      meladv2[j >> 4] |= (uint32_t)(first - cur2) << (2 * (j & 15));
+      const uint32_t cnt = (uint32_t)(first - cur2);
+      meladv2[nbt2 / 16 + (j >> 4)] |= cnt << (2 * (j & 15));
+      if (cnt == 1) meladv2[j >> 4] |= 1u << (j & 15);
+      if (cnt >= 2) meladv2[j >> 4] |= 0x10000u << (j & 15);
       cur2 = first;
       melw2[j] = make_float2(row[first], last > first ? row[last] : 0.f);
     }
@@ -1186,7 +1190,7 @@ size_t logmel_smem_bytes(const ttts_mel_plan* p) {
 
 size_t logmel2_smem_bytes(const ttts_mel_plan* p) {
   size_t s = (size_t)f2::kBStages2 * p->nb2 * 128 + (size_t)f2::kConvWarps2 * f2::kDepth * f2::kStageBytes +
-             (size_t)p->nbt2 * sizeof(float2) + (size_t)(p->nbt2 / 16 + 4) * 4 + 512 * 4 + kMaxMels * 4 +
+             (size_t)p->nbt2 * sizeof(float2) + (size_t)(2 * (p->nbt2 / 16) + 4) * 4 + 512 * 4 + kMaxMels * 4 +
              (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + sizeof(f2::Barriers) + 16;
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
 }
