@@ -37,9 +37,13 @@ constexpr int kPieceIters = (kPieces + 31) / 32;
 constexpr int kConvWarps2 = 4 * kSets;
 constexpr int kWarpConv02 = 4;
 constexpr int kWarpEpi02 = kWarpConv02 + kConvWarps2;
-constexpr int kThreads2 = (kWarpEpi02 + 4) * 32;
+constexpr int kEpiWarps = 4 * 4;                   // 4 lane quarters x kChains scan chains
+constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
+// registers per thread by role (setmaxnreg, per warpgroup): 128*40 + 384*96 + 512*40 = 62464 <= 65536; launch value 64
+constexpr int kRegsMisc = 40, kRegsConv = 96, kRegsEpi = 40;
 constexpr int kBStages2 = 4;                      // basis ring depth
 constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
+constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
 constexpr int kGroup = 32;                       // frames per group (one converter / epilogue warp)
 
 struct Params {
@@ -67,6 +71,8 @@ struct Params {
   float* dbg_reim;            // optional [total_frames][2*dbg_nbt], bins dbg_kmin..
   int dbg_nbt, dbg_kmin, kmax;
   int first_k[2];             // first live bin of each parity
+  int cstart[16];             // [passes][kChains] filter index of each scan chain's first bin
+  int cend[16];               // [passes][kChains] first of the two filters still open when the chain ends
   int exp_flags;
 };
 
@@ -113,14 +119,12 @@ __device__ __forceinline__ float ld_s(uint32_t addr) {
   return v;
 }
 
-// Rare event of the mel scan: `cnt` = 2 or 3 filters close before the next bin (narrow low-frequency filters).  Stores
-// the running pair and re-primes (run_lo, run_hi, next) from the parked sums of the filters that become active.
-// Out of line on purpose: the accumulator drain stays short; the common single close is predicated inline.
-__device__ __noinline__ float4 park_multi(uint32_t pa, float lo, float hi, float nx, uint32_t cnt) {
-  st_s(pa, lo);
-  st_s(pa + 4, hi);
-  if (cnt == 2) return make_float4(nx, ld_s(pa + 12), ld_s(pa + 16), 0.f);
-  return make_float4(ld_s(pa + 12), ld_s(pa + 16), ld_s(pa + 20), 0.f);
+// Rare event of the mel scan (two or three filters close before a bin: narrow low-frequency filters) and the close
+// of a chain: add the running pair to the parked sums with fresh loads (a neighbouring chain may have stored to the same
+// two slots).  Out of line on purpose, the accumulator drain stays short.
+__device__ __noinline__ void park_multi(uint32_t pa, float lo, float hi) {
+  st_s(pa, ld_s(pa) + lo);
+  st_s(pa + 4, ld_s(pa + 4) + hi);
 }
 
 }  // namespace f2
@@ -141,7 +145,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   float* s_norm = s_win + 512;                                       // [kMaxMels] mel_norms (or 1)
   float* s_park = s_norm + kMaxMels;                                 // [128][n_mels+1] raw mel sums of the tile
   const int park_pitch = P.n_mels + 1;
-  Barriers* bars = reinterpret_cast<Barriers*>(s_park + ((kTileM * park_pitch + 1) & ~1));
+  float* s_fl = s_park + ((kTileM * park_pitch + 1) & ~1);          // [2][kChains][lo,hi][128] open pairs at chain ends
+  Barriers* bars = reinterpret_cast<Barriers*>(s_fl + 2 * kChains * 2 * kTileM);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -158,7 +163,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     for (int i = 0; i < kBStages2; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
     for (int i = 0; i < kSets; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
     mbar_init(smem_u32(&bars->acc_full), 1);
-    mbar_init(smem_u32(&bars->acc_empty), 4);
+    mbar_init(smem_u32(&bars->acc_empty), kEpiWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpTmem) {
@@ -170,6 +175,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
 
+  const int wgroup = warp >> 2;                        // setmaxnreg works on warpgroups: misc | converters | epilogue
+  if (wgroup == 0) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsMisc));
   if (warp == kWarpTma) {
     // ===== basis producer: one bulk copy per k-step stage =====
     if (lane == 0 && !(P.exp_flags & 2)) {
@@ -178,7 +186,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         for (int ps = 0; ps < P.passes; ++ps)
           for (int ks = 0; ks < kKS; ++ks, ++seq) {
             const uint32_t st = seq % kBStages2, use = seq / kBStages2;
-            mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
+            mbar_wait<1>(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
             const uint32_t full = smem_u32(&bars->b_full[st]);
             mbar_expect_tx(full, b_stage_bytes);
             bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
@@ -198,11 +206,11 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     uint32_t as = 0, ause = 0;                                   // A stage = kseq % kSets, its use count
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        if (!(P.exp_flags & 4)) mbar_wait(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        if (!(P.exp_flags & 4)) mbar_wait<1>(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
         for (int ks = 0; ks < kKS; ++ks, ++kseq) {
           const uint32_t st = kseq % kBStages2, use = kseq / kBStages2;
-          if (!(P.exp_flags & 1)) mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
-          if (!(P.exp_flags & 2)) mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+          if (!(P.exp_flags & 1)) mbar_wait<1>(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+          if (!(P.exp_flags & 2)) mbar_wait<1>(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
           tc_fence_after();
           if (elect_one_sync()) {
             const uint32_t a_base = tmem + kColA2 + as * 32;
@@ -232,7 +240,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         }
       }
   }
-  else if (warp >= kWarpConv02 && warp < kWarpEpi02 && !(P.exp_flags & 1)) {
+  } else if (wgroup <= kSets) {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsConv));
+  if (!(P.exp_flags & 1)) {
     // ===== converters: stage own slots (cp.async) -> window + double fold + TF32 split -> TMEM A stage `set` =====
     const int cw = warp - kWarpConv02;
     const int set = cw >> 2;                           // A stage and k-step residue this warp serves
@@ -364,7 +374,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       }
       __syncwarp();                                    // every lane has its taps in registers: the stage can be refilled
       issue(stage);
-      mbar_wait(smem_u32(&bars->a_empty[set]), (mine & 1) ^ 1, P.status, 402);
+      mbar_wait<2>(smem_u32(&bars->a_empty[set]), (mine & 1) ^ 1, P.status, 402);
       tc_fence_after();
       tmem_st8(a_base + 0, ehi);
       tmem_st8(a_base + 8, elo);
@@ -381,161 +391,153 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
   }
-  else if (warp >= kWarpEpi02 && !(P.exp_flags & 4)) {
-    // ===== epilogue: power -> sparse mel (per parity) -> log(clamp) -> / norm =====
+  } else {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsEpi));
+  if (!(P.exp_flags & 4)) {
+    // ===== epilogue: power -> sparse mel -> log(clamp) -> / norm.  4 warps per TMEM lane quarter, one scan chain each =====
     const int q = warp & 3;
+    const int ch = (warp - kWarpEpi02) >> 2;           // my chain: bins [ch*cb, (ch+1)*cb) of every pass
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    const uint32_t t_re = tmem + lane_addr, t_im = t_re + kNBMax;
-    const int nblk = nb >> 4;
-    float nrm[4], rnrm[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      nrm[k] = (lane + 32 * k < P.n_mels) ? s_norm[lane + 32 * k] : 1.f;
-      rnrm[k] = 1.0f / nrm[k];
-    }
+    const int cb = nb / kChains;                       // bins per chain (multiple of 16)
+    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + kNBMax;
+    const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
+    const uint32_t bar_done = 1 + q, bar_flushed = 5 + q, bar_clean = 9 + q;   // named barriers of this quarter's four warps
     uint32_t pseq = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
-      const int t = gi.t0 + lane;
-      const bool valid = gi.valid && t < gi.T && t < P.Tmax;
-      float* orow = valid ? P.out + ((int64_t)gi.b * P.Tmax + t) * P.n_mels : nullptr;
-      int64_t gdbg = -1;
-      if (kDebug) { if (valid) gdbg = P.frame_off[gi.b] + t; }
-      // Running pair of adjacent filters (cur, cur+1) over the bins of ONE parity in ascending order.  The pair (and `nx`,
-      // the filter that becomes active next) is primed from the parked sums, so the second parity continues the first
-      // one's sums and every close is a plain store.  Host table: bit j = one filter closes before bin j (predicated
-      // inline), bit 16+j = two or three close (rare, out of line, count in the 2-bit table).
-      const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
-      uint32_t pa = pa0;
-      float run_lo = 0.f, run_hi = 0.f, nx = 0.f;      // parked sums are zero at the start of a tile
-      auto drain16x = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0, const uint32_t advw, auto multi) {
-        const float4* wp = reinterpret_cast<const float4*>(s_melw + bin0);
-#pragma unroll
-        for (int j2 = 0; j2 < 8; ++j2) {
-          const float4 w2 = wp[j2];
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int j = 2 * j2 + h;
-            if (decltype(multi)::value && (advw & (0x10000u << j))) {   // warp-uniform, rare
-              const uint32_t cnt = (s_adv2[bin0 >> 4] >> (2 * j)) & 3u;
-              const float4 t4 = park_multi(pa, run_lo, run_hi, nx, cnt);
-              run_lo = t4.x; run_hi = t4.y; nx = t4.z;
-              pa += 4 * cnt;
+      // Sparse mel contraction.  Every bin feeds the running pair of adjacent filters (cur, cur+1) of its chain; the host
+      // table says how many filters close before each bin (bit j: one, predicated inline; bit 16+j: two or three, rare,
+      // out of line).  A closed filter's partial sum is added to its parked sum (`old`, prefetched one close ahead; the
+      // park rows start a tile zeroed).  The filters still open at the end of a chain are shared with the next chain, so
+      // they go through s_fl and chain 0's warp adds them once all four chains of the quarter are done.
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        float run_lo = 0.f, run_hi = 0.f;
+        uint32_t pa = pa0 + 4u * (uint32_t)P.cstart[ps * kChains + ch];
+        float old = ld_s(pa);
+        const int bin_base = ps * nb + ch * cb;
+        mbar_wait<3>(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
+        tc_fence_after();
+        for (int r16 = 0; r16 < cb; r16 += 16) {
+          const uint32_t advw = s_adv[(bin_base + r16) >> 4];
+#pragma unroll 1
+          for (int qr = 0; qr < 4; ++qr) {             // not unrolled: the scan stays resident in the instruction cache
+            uint32_t re[4], im[4];
+            tmem_ld4(t_re + r16 + 4 * qr, re);
+            tmem_ld4(t_im + r16 + 4 * qr, im);
+            tmem_wait_ld();
+            if (r16 + 16 >= cb && qr == 3) {           // my accumulator columns are in registers: hand them back
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
             }
-            if (advw & (1u << j)) {                      // warp-uniform: one filter closes before this bin
-              st_s(pa, run_lo);
-              run_lo = run_hi; run_hi = nx;
-              nx = ld_s(pa + 12);
-              pa += 4;
-            }
-            const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
-            float pw = fmaf(a, a, bq * bq);
-            if (kPower1) pw = sqrtf(pw + P.power_eps);
-            run_lo = fmaf(h ? w2.z : w2.x, pw, run_lo);
-            run_hi = fmaf(h ? w2.w : w2.y, pw, run_hi);
-          }
-        }
-      };
-      // blocks without a multi-close (all but the lowest one or two of a parity) run the branch-free variant
-      auto drain16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int bin0) {
-        const uint32_t advw = s_adv[bin0 >> 4];
-        if (advw >> 16) drain16x(re, im, bin0, advw, std::true_type{});
-        else drain16x(re, im, bin0, advw, std::false_type{});
-      };
-      auto dump16 = [&](const uint32_t (&re)[16], const uint32_t (&im)[16], int ps, int blk) {
-        if (kDebug) {
-          if (gdbg >= 0) {
-            const int par = ps / P.sp, sub = ps - par * P.sp;
+            if (kDebug) {
+              const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
+              const int t = gi.t0 + lane;
+              if (gi.valid && t < gi.T && t < P.Tmax) {
+                const int64_t gdbg = P.frame_off[gi.b] + t;
+                const int par = ps / P.sp, sub = ps - par * P.sp;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int k = P.first_k[par] + 2 * (sub * nb + blk * 16 + j);
-              if (k <= P.kmax) {
-                float* d = P.dbg_reim + gdbg * (2 * P.dbg_nbt) + (k - P.dbg_kmin);
-                d[0] = __uint_as_float(re[j]);
-                d[P.dbg_nbt] = __uint_as_float(im[j]);
+                for (int j = 0; j < 4; ++j) {
+                  const int k = P.first_k[par] + 2 * (sub * nb + ch * cb + r16 + 4 * qr + j);
+                  if (k <= P.kmax) {
+                    float* d = P.dbg_reim + gdbg * (2 * P.dbg_nbt) + (k - P.dbg_kmin);
+                    d[0] = __uint_as_float(re[j]);
+                    d[P.dbg_nbt] = __uint_as_float(im[j]);
+                  }
+                }
               }
             }
-          }
-        }
-      };
-      auto release_acc = [&]() {        // accumulators of this pass are in registers: hand TMEM back to the MMA warp
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
-      };
-      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        if (ps == P.sp) {               // second parity: close the first one, restart the scan on top of its sums
-          st_s(pa, run_lo); st_s(pa + 4, run_hi);
-          pa = pa0;
-          run_lo = ld_s(pa); run_hi = ld_s(pa + 4); nx = ld_s(pa + 8);
-        }
-        mbar_wait(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
-        tc_fence_after();
-        uint32_t reA[16], imA[16], reB[16], imB[16];
-        tmem_ld16(t_re, reA);
-        tmem_ld16(t_im, imA);
-        for (int blk = 0; blk < nblk; blk += 2) {
-          tmem_wait_ld();                                          // set A = block blk
-          if (blk + 1 < nblk) {
-            tmem_ld16(t_re + (blk + 1) * 16, reB);
-            tmem_ld16(t_im + (blk + 1) * 16, imB);
-          } else {
-            release_acc();
-          }
-          dump16(reA, imA, ps, blk);
-          if (!(P.exp_flags & 8)) drain16(reA, imA, ps * nb + blk * 16);
-          if (blk + 1 < nblk) {
-            tmem_wait_ld();                                        // set B = block blk+1
-            if (blk + 2 < nblk) {
-              tmem_ld16(t_re + (blk + 2) * 16, reA);
-              tmem_ld16(t_im + (blk + 2) * 16, imA);
-            } else {
-              release_acc();
-            }
-            dump16(reB, imB, ps, blk + 1);
-            if (!(P.exp_flags & 8)) drain16(reB, imB, ps * nb + (blk + 1) * 16);
-          }
-        }
-      }
-      st_s(pa, run_lo); st_s(pa + 4, run_hi);   // close the running pair
-      // raw mel sums -> log(max(., clamp)) / norm: coalesced output rows, 4 rows x up to 4 columns per lane in flight
-      // (independent logf / division chains), and the park rows are handed back zeroed for the next tile
-      __syncwarp();
-      for (int rr0 = 0; rr0 < ((P.exp_flags & 16) ? 0 : 32); rr0 += 4) {
-        float* rowp[4];
-        float v[4][4];
+            if (P.exp_flags & 8) continue;
+            const uint32_t advq = advw >> (4 * qr);
+            const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin_base + r16 + 4 * qr);
+            const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin_base + r16 + 4 * qr + 2);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          rowp[i] = reinterpret_cast<float*>((uintptr_t)__shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr0 + i));
-          float* parked = s_park + (q * 32 + rr0 + i) * park_pitch + lane;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            v[i][k] = 1.f;
-            if (lane + 32 * k < P.n_mels) { v[i][k] = parked[32 * k]; parked[32 * k] = 0.f; }
-          }
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          if (32 * k < P.n_mels) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              // x / norm as reciprocal + one Newton correction: branch-free (the IEEE division's slow-path call would
-              // serialise the independent chains) and equal to the correctly rounded quotient except in rare last-bit ties
-              const float x = logf(fmaxf(v[i][k], P.clamp));
-              const float y = x * rnrm[k];
-              v[i][k] = fabsf(y) < 3.0e38f ? fmaf(fmaf(-y, nrm[k], x), rnrm[k], y) : y;   // norm 0 / inf: keep x * (1/norm)
+            for (int j = 0; j < 4; ++j) {
+              if (advq & (0x10000u << j)) {            // warp-uniform, rare: two or three filters close
+                const uint32_t cnt = (s_adv2[(bin_base + r16) >> 4] >> (2 * (4 * qr + j))) & 3u;
+                park_multi(pa, run_lo, run_hi);
+                run_lo = 0.f; run_hi = 0.f;
+                pa += 4 * cnt;
+                old = ld_s(pa);
+              }
+              if (advq & (1u << j)) {                  // warp-uniform: one filter closes before this bin
+                st_s(pa, old + run_lo);
+                run_lo = run_hi; run_hi = 0.f;
+                pa += 4;
+                old = ld_s(pa);                        // consumed at the next close
+              }
+              const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
+              float pw = fmaf(a, a, bq * bq);
+              if (kPower1) pw = sqrtf(pw + P.power_eps);
+              const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
+              const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
+              run_lo = fmaf(wl, pw, run_lo);
+              run_hi = fmaf(wh, pw, run_hi);
             }
           }
         }
+        // the pair still open at the end of my chain
+        float* fl = s_fl + ((pseq & 1) * kChains + ch) * 2 * kTileM + r;
+        fl[0] = run_lo;
+        fl[kTileM] = run_hi;
+        if (ch != 0) {
+          asm volatile("bar.arrive %0, 128;" ::"r"(bar_done) : "memory");
+        } else {
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_done) : "memory");
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+          for (int c = 0; c < kChains; ++c) {
+            const float* f = s_fl + ((pseq & 1) * kChains + c) * 2 * kTileM + r;
+            park_multi(pa0 + 4u * (uint32_t)P.cend[ps * kChains + c], f[0], f[kTileM]);
+          }
+        }
+        // nobody starts the next scan (or the log pass) before the open pairs are in the park rows
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_flushed) : "memory");
+        if (ps == P.passes - 1) {
+          // raw mel sums -> log(max(., clamp)) / norm.  Each of the quarter's four warps takes 8 of its 32 rows: coalesced
+          // output rows, 2 rows x up to 4 columns per lane in flight (independent logf / division chains); the park rows
+          // are handed back zeroed for the next tile
+          const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
+          const int t = gi.t0 + lane;
+          float* orow = (gi.valid && t < gi.T && t < P.Tmax) ? P.out + ((int64_t)gi.b * P.Tmax + t) * P.n_mels : nullptr;
+          for (int rr0 = 8 * ch; rr0 < ((P.exp_flags & 16) ? 0 : 8 * ch + 8); rr0 += 2) {
+            float* rowp[2];
+            float v[2][4];
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (rowp[i] && lane + 32 * k < P.n_mels) rowp[i][lane + 32 * k] = v[i][k];
+            for (int i = 0; i < 2; ++i) {
+              rowp[i] = reinterpret_cast<float*>((uintptr_t)__shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr0 + i));
+              float* parked = s_park + (q * 32 + rr0 + i) * park_pitch + lane;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                v[i][k] = 1.f;
+                if (lane + 32 * k < P.n_mels) { v[i][k] = parked[32 * k]; parked[32 * k] = 0.f; }
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (32 * k < P.n_mels) {
+                const float nrm = (lane + 32 * k < P.n_mels) ? s_norm[lane + 32 * k] : 1.f, rn = 1.0f / nrm;
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                  // x / norm as reciprocal + one Newton correction: branch-free (the IEEE division's slow-path call
+                  // would serialise the chains) and equal to the correctly rounded quotient except in rare last-bit ties
+                  const float x = logf(fmaxf(v[i][k], P.clamp));
+                  const float y = x * rn;
+                  v[i][k] = fabsf(y) < 3.0e38f ? fmaf(fmaf(-y, nrm, x), rn, y) : y;   // norm 0 / inf: keep x * (1/norm)
+                }
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (rowp[i] && lane + 32 * k < P.n_mels) rowp[i][lane + 32 * k] = v[i][k];
+          }
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_clean) : "memory");   // all 32 park rows of the quarter are zero again
+        }
       }
-      __syncwarp();
     }
+  }
+
   }
 
   // ---- teardown

@@ -64,6 +64,7 @@ constexpr int kAStages = 4;
 constexpr int kThreads = 512;
 constexpr int kMaxMels = 128;
 constexpr long long kTimeoutCycles = 4000000000LL;
+constexpr int f2_kChains = 4;          // mel-scan chains per epilogue thread of k_logmel2 (== f2::kChains)
 
 // warp roles of k_logmel
 constexpr int kWarpTma = 0, kWarpMma = 1, kWarpTmem = 2;   // warp 3 is spare
@@ -124,6 +125,8 @@ struct ttts_mel_plan {
   int nb2 = 0;         // bins per pass
   int nbt2 = 0;        // 2 * sp * nb2
   float wc = 0.f;      // centre tap weight w[512] * spec_scale
+  int cstart[16] = {0};  // [2 sp][4 chains] filter index of each mel-scan chain's first bin
+  int cend[16] = {0};    // ... and of the first of the two filters still open at its end
   float* d_basis2 = nullptr;   // [2 sp][33 k-steps][4 arrays][2 k-halves][nb2][4] fp32 (TF32-exact values), no window
   float2* d_melw2 = nullptr;   // [nbt2]
   uint32_t* d_meladv2 = nullptr;  // [nbt2/16], 2 bits per bin
@@ -266,26 +269,35 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   for (int q = 0; q < 2; ++q) n_par[q] = p->first_k[q] <= kmax ? (kmax - p->first_k[q]) / 2 + 1 : 0;
   const int n_par_max = n_par[0] > n_par[1] ? n_par[0] : n_par[1];
   p->sp = (n_par_max + kNBMax - 1) / kNBMax;
-  p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 16);
+  p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 64);   // 4 scan chains of whole 16-bin blocks
   p->nbt2 = 2 * p->sp * p->nb2;
   if (const char* e2 = getenv("TTTS_MEL_ALGO")) p->algo = atoi(e2) == 1 ? 1 : 2;
   const int nb2 = p->nb2, nbt2 = p->nbt2, per_par = p->sp * p->nb2;
   std::vector<float2> melw2(nbt2, make_float2(0.f, 0.f));
   std::vector<uint32_t> meladv2(2 * (nbt2 / 16), 0u);   // [0]: single / multi close masks, [1]: 2-bit counts
+  const int chain_bins = nb2 / f2_kChains;
   for (int par = 0; par < 2; ++par) {
     int cur2 = 0;
     for (int idx = 0; idx < per_par; ++idx) {
       const int k = p->first_k[par] + 2 * idx, j = par * per_par + idx;
-      if (k > kmax) break;
-      const float* row = fb + (size_t)k * nm;
+      const bool chain_start = idx % chain_bins == 0;
       int first = -1, last = -1;
-      for (int m = 0; m < nm; ++m)
-        if (row[m] != 0.f) { if (first < 0) first = m; last = m; }
-      if (first < 0) continue;
-      if (last - first > 1 || first < cur2 || first - cur2 > 3) {
+      if (k <= kmax) {
+        const float* row = fb + (size_t)k * nm;
+        for (int m = 0; m < nm; ++m)
+          if (row[m] != 0.f) { if (first < 0) first = m; last = m; }
+      }
+      if (first >= 0 && (last - first > 1 || first < cur2 || first - cur2 > 3)) {
         delete p;
         return fail(TTTS_MEL_EINVAL, "filterbank row %d: need <= two adjacent, non-decreasing filters per bin", k);
       }
+      if (chain_start) {                      // a scan chain starts on this bin's own first filter: nothing closes before it
+        if (idx > 0) p->cend[j / chain_bins - 1] = cur2;   // the previous chain ends with (cur2, cur2 + 1) open
+        if (first >= 0) cur2 = first;
+        p->cstart[j / chain_bins] = cur2;
+      }
+      if (first < 0) continue;
+      const float* row = fb + (size_t)k * nm;
       const uint32_t cnt = (uint32_t)(first - cur2);
       meladv2[nbt2 / 16 + (j >> 4)] |= cnt << (2 * (j & 15));
       if (cnt == 1) meladv2[j >> 4] |= 1u << (j & 15);
@@ -293,6 +305,7 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
       cur2 = first;
       melw2[j] = make_float2(row[first], last > first ? row[last] : 0.f);
     }
+    p->cend[(par + 1) * per_par / chain_bins - 1] = cur2;
   }
   std::vector<float> win2(512, 0.f);
   for (int n = 1; n <= 256; ++n) {
@@ -455,20 +468,25 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
       : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok;
 }
-// Bounded wait: a pipeline bug must surface as an error code, never as a hung GPU.
-__device__ __noinline__ void mbar_timeout(int32_t* status, int code) {
+// Bounded wait: a pipeline bug must surface as an error code, never as a hung GPU.  The slow path is out of line (the
+// wait sites stay two instructions long); kRole gives every register-budget region of k_logmel2 (setmaxnreg) its own
+// copy, because ptxas compiles a function shared by several regions for the smallest of their budgets -- and then the
+// callers too.
+__device__ __forceinline__ void mbar_timeout(int32_t* status, int code) {
   atomicExch(status, code);
   __threadfence_system();
   __trap();
 }
+template <int kRole>
 __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, int32_t* status, int code) {
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
   }
 }
+template <int kRole = 0>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int32_t* status, int code) {
-  if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity, status, code);
+  if (!mbar_try_wait(bar, parity)) mbar_wait_slow<kRole>(bar, parity, status, code);
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -507,6 +525,16 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
       "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
         "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t* v) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
       : "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -1191,7 +1219,7 @@ size_t logmel_smem_bytes(const ttts_mel_plan* p) {
 size_t logmel2_smem_bytes(const ttts_mel_plan* p) {
   size_t s = (size_t)f2::kBStages2 * p->nb2 * 128 + (size_t)f2::kConvWarps2 * f2::kDepth * f2::kStageBytes +
              (size_t)p->nbt2 * sizeof(float2) + (size_t)(2 * (p->nbt2 / 16) + 4) * 4 + 512 * 4 + kMaxMels * 4 +
-             (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + sizeof(f2::Barriers) + 16;
+             (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + (size_t)2 * f2::kChains * 2 * kTileM * 4 + sizeof(f2::Barriers) + 16;
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
 }
 
@@ -1240,6 +1268,8 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.clamp = p->cfg.clamp; P.power_eps = p->cfg.power_eps; P.status = w.status;
     P.dbg_reim = dbg_reim; P.dbg_nbt = p->nbt; P.dbg_kmin = p->kmin; P.kmax = p->kmax;
     P.first_k[0] = p->first_k[0]; P.first_k[1] = p->first_k[1];
+    for (int i = 0; i < 16; ++i) { P.cstart[i] = p->cstart[i]; P.cend[i] = p->cend[i]; }
+    static_assert(f2_kChains == f2::kChains, "chain count");
     P.exp_flags = g_exp_flags;
     const size_t smem = logmel2_smem_bytes(p);
     const bool pw1 = p->cfg.power == 1.0f;
