@@ -26,7 +26,8 @@
 
 namespace f2 {
 
-constexpr int kSets = 3;                         // converter sets == A-operand TMEM stages
+constexpr int kSets = 3;                         // converter sets: set s serves the k-steps with sequence number == s (mod 3)
+constexpr int kAStages2 = 4;                     // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
 constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
 constexpr int kSlotFloats = 20;                  // 12 forward taps + 8 mirrored taps; 80 B pitch: conflict-free LDS.128
@@ -78,7 +79,7 @@ struct Params {
 
 struct __align__(8) Barriers {
   uint64_t b_full[kBStages2], b_empty[kBStages2];
-  uint64_t a_full[kSets], a_empty[kSets];
+  uint64_t a_full[kAStages2], a_empty[kAStages2];
   uint64_t acc_full, acc_empty;
 };
 
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   for (int i = threadIdx.x; i < kTileM * park_pitch; i += kThreads2) s_park[i] = 0.f;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStages2; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
-    for (int i = 0; i < kSets; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
+    for (int i = 0; i < kAStages2; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
     mbar_init(smem_u32(&bars->acc_full), 1);
     mbar_init(smem_u32(&bars->acc_empty), kEpiWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
     const uint32_t d_re = tmem, d_im = tmem + kNBMax;
     uint32_t kseq = 0, pseq = 0;
-    uint32_t as = 0, ause = 0;                                   // A stage = kseq % kSets, its use count
+    uint32_t as = 0, ause = 0;                                   // A stage = kseq % kAStages2, its use count
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         if (!(P.exp_flags & 4)) mbar_wait<1>(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             if (ks == kKS - 1) tc_commit(smem_u32(&bars->acc_full));
           }
           __syncwarp();
-          if (++as == kSets) { as = 0; ++ause; }
+          if (++as == kAStages2) { as = 0; ++ause; }
         }
       }
   }
@@ -244,6 +245,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsConv));
   if (!(P.exp_flags & 1)) {
     // ===== converters: stage own slots (cp.async) -> window + double fold + TF32 split -> TMEM A stage `set` =====
+    const float *src_p = P.src, *edge_p = P.edge;
     const int cw = warp - kWarpConv02;
     const int set = cw >> 2;                           // A stage and k-step residue this warp serves
     const int q = warp & 3;                            // TMEM lane quarter == group within the tile
@@ -271,10 +273,12 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 
     int32_t off[kPieceIters];
     uint32_t okm = 0, edm = 0;
+    bool plain = false;                                // every live piece of the warp is valid and read from P.src
     float xc_next = 0.f;                               // centre tap f[512] of this lane's row in the issue tile
     auto load_tile = [&](int tile) {
       okm = edm = 0;
       xc_next = 0.f;
+      plain = false;
       if (tile >= num_tiles) return;
       const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
       if (!gi.valid) return;
@@ -290,11 +294,15 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         okm |= (uint32_t)ok << i;
         edm |= (uint32_t)(ok && edge) << i;
       }
+      uint32_t live = 0;
+#pragma unroll
+      for (int i = 0; i < kPieceIters; ++i) live |= (pc_dst[i] >> 31) << i;
+      plain = __all_sync(0xffffffffu, okm == live && edm == 0);
       const int t = gi.t0 + lane;
       if (t < gi.T) {
         bool edge;
         const int32_t o = sample_offset(P, gi.b, gi.T, t, kNfft / 2, &edge);
-        xc_next = __ldg((edge ? P.edge : P.src) + o);
+        xc_next = __ldg((edge ? edge_p : src_p) + o);
       }
     };
 
@@ -303,13 +311,23 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       if (ic.tile < num_tiles && ic.ks < kKS - 1) {
         const uint32_t base = smem_u32(my_raw + (size_t)stage * kStageBytes);
         const int adv = kKStep * ic.ks;
+        if (plain) {                                   // warp-uniform: interior groups (all but the first / last of a clip)
 #pragma unroll
-        for (int i = 0; i < kPieceIters; ++i) {
-          if (pc_dst[i] >> 31) {
-            const bool ok = (okm >> i) & 1u;
-            const bool fwd = ((pc_dst[i] >> 16) & 7) < 3;
-            const float* bp = ((edm >> i) & 1u) ? P.edge : P.src;
-            cp_async16(base + (pc_dst[i] & 0xffffu), ok ? bp + (off[i] + (fwd ? adv : -adv)) : P.src, ok ? 16u : 0u);
+          for (int i = 0; i < kPieceIters; ++i) {
+            if (i < kPieces / 32 || (pc_dst[i] >> 31)) {
+              const bool fwd = ((pc_dst[i] >> 16) & 7) < 3;
+              cp_async16(base + (pc_dst[i] & 0xffffu), src_p + (off[i] + (fwd ? adv : -adv)), 16u);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < kPieceIters; ++i) {
+            if (pc_dst[i] >> 31) {
+              const bool ok = (okm >> i) & 1u;
+              const bool fwd = ((pc_dst[i] >> 16) & 7) < 3;
+              const float* bp = ((edm >> i) & 1u) ? edge_p : src_p;
+              cp_async16(base + (pc_dst[i] & 0xffffu), ok ? bp + (off[i] + (fwd ? adv : -adv)) : src_p, ok ? 16u : 0u);
+            }
           }
         }
       }
@@ -323,8 +341,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     for (int d = 0; d < kDepth; ++d) issue(d);
 
     Cursor cc{(int)blockIdx.x, 0, set};
-    uint32_t mine = 0;
-    const uint32_t a_base = tmem + lane_addr + kColA2 + set * 32;
+    uint32_t mine = 0, kseq = set;                     // kseq: sequence number of my current k-step (A stage = kseq % 4)
     while (cc.tile < num_tiles) {
       const uint32_t stage = mine % kDepth;
       asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
@@ -374,7 +391,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       }
       __syncwarp();                                    // every lane has its taps in registers: the stage can be refilled
       issue(stage);
-      mbar_wait<2>(smem_u32(&bars->a_empty[set]), (mine & 1) ^ 1, P.status, 402);
+      const uint32_t as = kseq % kAStages2, ause = kseq / kAStages2;
+      const uint32_t a_base = tmem + lane_addr + kColA2 + as * 32;
+      mbar_wait<2>(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
       tc_fence_after();
       tmem_st8(a_base + 0, ehi);
       tmem_st8(a_base + 8, elo);
@@ -385,8 +404,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[set]));
+      if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
       ++mine;
+      kseq += kSets;
       if (advance(cc)) xc = xc_next;
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
