@@ -335,3 +335,44 @@ def test_v3_librosa_style_mel_spectrogram(dev):
         assert np.abs(_np(y) - ref).max() <= TOL, L
     y2 = mel_spectrogram(torch.from_numpy(x).to(dev), 1024, 80, 24000, 256, 1024, 0, 8000, center=False)
     assert torch.equal(y, y2)
+
+
+def test_group_layout_frame_counts_around_multiples_of_32(dev, v1):
+    """k_logmel2 lays clips out in groups of 32 frames (one converter / epilogue warp each): frame counts just
+    below, at and above group boundaries, partly empty last groups, and tiles whose four groups belong to
+    different clips must all equal the per-clip oracle (k_logmel2.cuh; frame count torch functional.py:648)."""
+    frames = [3, 8, 9, 12, 31, 32, 33, 34, 63, 64, 65, 96, 127, 128, 129, 160]
+    lens = [256 * (t - 1) + 7 * (i % 5) for i, t in enumerate(frames)]      # T = 1 + L // 256
+    lens[0] = 513
+    x = orc.synth("gauss", len(lens), max(lens), 4242)
+    y, nf, mask = v1(torch.from_numpy(x).to(dev), lengths=torch.tensor(lens))
+    ry, rn, rmask = orc.callsite_logmel_ragged(x, lens, orc.V1, orc.default_mel_norms(80))
+    assert nf.cpu().tolist() == rn.tolist() == [1 + L // 256 for L in lens]
+    assert np.array_equal(_np(mask), rmask)
+    assert np.abs(_np(y) - ry.numpy()).max() <= TOL
+
+
+def test_double_fold_kernel_agrees_with_single_fold_kernel(dev, monkeypatch):
+    """Two independent tcgen05 kernels in the library: k_logmel (K = 512, window in the basis) and the default
+    k_logmel2 (K = 256 + centre tap, even / odd bin passes, window in the converter).  Same inputs -> both within
+    TOL of the oracle and within 2 TOL of each other, dense and ragged, V1 and V2."""
+    from xtts_b200 import MelPlan
+    kw1 = dict(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
+               power=2.0, norm="slaney")
+    kw2 = dict(sample_rate=24000, n_fft=1024, hop_length=256, win_length=1024, n_mels=100, f_min=0, f_max=None,
+               power=1.0, norm=None, clamp=1e-7)
+    x = torch.from_numpy(orc.synth("uniform", 6, 40000, 77)).to(dev)
+    lens = torch.tensor([40000, 513, 8192, 30001, 12345, 39999])
+    for kw in (kw1, kw2):
+        outs = []
+        for algo in ("1", "2"):
+            monkeypatch.setenv("TTTS_MEL_ALGO", algo)      # read by ttts_mel_plan_create
+            plan = MelPlan(device=dev, **kw)
+            dense = plan.forward(x)[0]
+            rag = plan.forward(x, lens.to(dev))[0]
+            torch.cuda.synchronize()
+            outs.append((_np(dense), _np(rag)))
+        for a, b in zip(outs[0], outs[1]):
+            assert a.shape == b.shape
+            assert np.abs(a - b).max() <= 2 * TOL
+    monkeypatch.delenv("TTTS_MEL_ALGO")

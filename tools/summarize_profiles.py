@@ -46,7 +46,7 @@ wr = [f(v) for v in met["dram__bytes_write.sum"]["per_launch"]]
 scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1}
 rb = sum(rd) / len(rd) * scale[met["dram__bytes_read.sum"]["unit"]]
 wb = sum(wr) / len(wr) * scale[met["dram__bytes_write.sum"]["unit"]]
-summary = {"kernel": "k_logmel<false,false>", "workload": "64x10s (55168 frames) per launch", "source": os.path.basename(rep),
+summary = {"kernel": "k_logmel2<false,false>", "workload": "64x10s (55168 frames) per launch", "source": os.path.basename(rep),
            "dram_bytes_per_launch": rb + wb, "dram_read_bytes": rb, "dram_write_bytes": wb,
            "algorithmic_bytes_per_launch": 55168 * 1344, "metrics": met}
 json.dump(summary, open(os.path.join(out_dir, "k_logmel_ncu_metrics.json"), "w"), indent=1)

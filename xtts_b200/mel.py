@@ -114,7 +114,7 @@ class MelPlan:
             raise RuntimeError(f"input on {wav.device}, plan on {self.device}")
         if wav.dtype != torch.float32 or wav.dim() != 2:
             raise RuntimeError("MelPlan.forward expects a 2-D float32 tensor")
-        if wav.stride(1) != 1 or wav.stride(0) < wav.shape[1]:
+        if wav.stride(1) != 1 or (wav.shape[0] > 1 and wav.stride(0) < wav.shape[1]):
             wav = wav.contiguous()
         B, Lmax = int(wav.shape[0]), int(wav.shape[1])
         if B == 0:
@@ -133,7 +133,9 @@ class MelPlan:
             n_frames = torch.empty((B,), dtype=torch.int32, device=self.device)
             mask = torch.empty((B, T), dtype=torch.uint8, device=self.device) if want_mask else None
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            args = [self._h, wav.data_ptr(), int(wav.stride(0)), len_dev.data_ptr() if len_dev is not None else None,
+            # a size-1 batch dimension may carry any stride (torch treats it as contiguous): the row stride is moot
+            row_stride = int(wav.stride(0)) if B > 1 else Lmax
+            args = [self._h, wav.data_ptr(), row_stride, len_dev.data_ptr() if len_dev is not None else None,
                     B, Lmax, T, out.data_ptr(), n_frames.data_ptr(), mask.data_ptr() if mask is not None else None,
                     ws.data_ptr(), ws_bytes, stream]
             reim = None
