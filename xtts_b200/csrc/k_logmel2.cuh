@@ -151,8 +151,6 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t total_groups = P.group_off[P.B];
-  const int num_tiles = (int)((total_groups + 3) / 4);
 
   // ---- one-time setup
   for (int i = threadIdx.x; i < P.nbt; i += kThreads2) s_melw[i] = P.melw[i];
@@ -171,10 +169,15 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  // Programmatic dependent launch: everything above (plan constants, barriers, TMEM) overlaps k_prep, which produces
+  // the frame counts, group prefix and edge buffers read below.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
+  const int64_t total_groups = P.group_off[P.B];
+  const int num_tiles = (int)((total_groups + 3) / 4);
 
   const int wgroup = warp >> 2;                        // setmaxnreg works on warpgroups: misc | converters | epilogue
   if (wgroup == 0) {

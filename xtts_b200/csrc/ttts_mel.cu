@@ -567,9 +567,10 @@ __device__ __forceinline__ long long clip_frames(long long L, long long Lmax, in
   return T;
 }
 
+constexpr int kPrepSplit = 4;            // blocks per clip for the side work
 __device__ void clip_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
                           int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, float* __restrict__ out, int n_mels,
-                          uint8_t* __restrict__ mask, int b);
+                          uint8_t* __restrict__ mask, int b, int part);
 
 // Block 0: frame counts + prefix.  Blocks 1..B: per-clip side work of clip blockIdx.x-1 -- its edge buffer (when `edge`
 // is given), zeros for its padded output frames (ragged batches) and its row of the padding mask (when `mask` is given).
@@ -579,11 +580,28 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
                                                int Tmax, int32_t* __restrict__ n_frames,
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
                                                int64_t* __restrict__ group_off, int32_t* __restrict__ status) {
-  if (blockIdx.x > 0) { clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, blockIdx.x - 1); return; }
+  asm volatile("griddepcontrol.launch_dependents;");   // the fused kernel may start its prologue (it waits for this grid's end)
+  if (blockIdx.x > 0) {
+    clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, (blockIdx.x - 1) / kPrepSplit,
+              (blockIdx.x - 1) % kPrepSplit);
+    return;
+  }
   __shared__ long long part[1024];
   const int tid = threadIdx.x;
   if (tid == 0) *status = 0;
   __syncthreads();
+  if (!lengths) {                           // dense batch: closed forms, no scan
+    int err = 0;
+    const long long T = clip_frames(Lmax, Lmax, pad, Tmax, &err);
+    if (err && tid == 0) atomicExch(status, err);
+    const long long G = (T + 31) >> 5;
+    for (int b = tid; b <= B; b += 1024) {
+      if (b < B) { n_frames[b] = (int32_t)T; if (n_frames_user) n_frames_user[b] = (int32_t)T; }
+      frame_off[b] = T * b;
+      group_off[b] = G * b;
+    }
+    return;
+  }
   const int per = (B + 1023) / 1024;
   const int b0 = tid * per, b1 = min(B, b0 + per);
   long long sum = 0;
@@ -667,8 +685,9 @@ __global__ void __launch_bounds__(256) k_pad(const float* __restrict__ wav, int6
 // ------------------------------------------------------------------------------------------
 __device__ void clip_body(const float* __restrict__ wav, int64_t row_stride, const int64_t* __restrict__ lengths,
                           int64_t Lmax, int pad, int Tmax, float* __restrict__ edge, float* __restrict__ out, int n_mels,
-                          uint8_t* __restrict__ mask, int b) {
+                          uint8_t* __restrict__ mask, int b, int part) {
   const int64_t L = lengths ? lengths[b] : Lmax;
+  const int tid = part * blockDim.x + threadIdx.x, nthr = kPrepSplit * blockDim.x;
   int err = 0;
   const int T = (int)clip_frames(L, Lmax, pad, Tmax, &err);
   if (edge) {
@@ -676,7 +695,7 @@ __device__ void clip_body(const float* __restrict__ wav, int64_t row_stride, con
     float* __restrict__ dst = edge + (int64_t)b * kEdgeClip;
     const bool okL = T > 0 && err != 1;
     const int64_t startB = (int64_t)kHop * (T - 4);
-    for (int i = threadIdx.x; i < kEdgeClip; i += blockDim.x) {
+    for (int i = tid; i < kEdgeClip; i += nthr) {
       const bool inB = i >= kEdgeA;
       int64_t s = (inB ? startB + (i - kEdgeA) : (int64_t)i) - pad;
       float v = 0.f;
@@ -691,11 +710,11 @@ __device__ void clip_body(const float* __restrict__ wav, int64_t row_stride, con
   if (out && lengths) {          // collate contract (ttts/gpt/dataset.py:116-117): frames t >= n_frames[b] are 0.0
     float* __restrict__ z = out + ((int64_t)b * Tmax + T) * n_mels;
     const int64_t n = (int64_t)(Tmax - T) * n_mels;
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) z[i] = 0.f;
+    for (int64_t i = tid; i < n; i += nthr) z[i] = 0.f;
   }
   if (mask) {                    // make_pad_mask (ttts/utils/utils.py:77-103)
     uint8_t* __restrict__ mrow = mask + (int64_t)b * Tmax;
-    for (int t = threadIdx.x; t < Tmax; t += blockDim.x) mrow[t] = t >= T ? 1 : 0;
+    for (int t = tid; t < Tmax; t += nthr) mrow[t] = t >= T ? 1 : 0;
   }
 }
 
@@ -1237,7 +1256,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   // the reflect padding go through a small edge buffer.  Otherwise (and for k_simt) the clips are padded
   // into the workspace first.
   const bool direct = impl == Impl::Tcgen05 && vec_ok && (int64_t)B * row_stride < ((int64_t)1 << 31);
-  k_prep<<<B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
+  k_prep<<<kPrepSplit * B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
                                      p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status);
   ++g_launches;
   if (!direct) {
@@ -1273,7 +1292,16 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
     if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
-    kern<<<p->num_sms, f2::kThreads2, smem, stream>>>(P);
+    {
+      // programmatic dependent launch behind k_prep: the prologue of the persistent kernel overlaps it
+      cudaLaunchConfig_t lc{};
+      lc.gridDim = dim3((unsigned)p->num_sms); lc.blockDim = dim3(f2::kThreads2); lc.dynamicSmemBytes = smem; lc.stream = stream;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      lc.attrs = at; lc.numAttrs = 1;
+      CUDA_TRY(cudaLaunchKernelEx(&lc, kern, P));
+    }
     if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
     ++g_launches;
   } else if (impl == Impl::Tcgen05) {
