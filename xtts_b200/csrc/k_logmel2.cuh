@@ -42,7 +42,8 @@ constexpr int kEpiWarps = 4 * 4;                   // 4 lane quarters x kChains 
 constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
 // registers per thread by role (setmaxnreg, per warpgroup): 128*40 + 384*96 + 512*40 = 62464 <= 65536; launch value 64
 constexpr int kRegsMisc = 40, kRegsConv = 96, kRegsEpi = 40;
-constexpr int kBStages2 = 4;                      // basis ring depth
+constexpr int kBStages2 = 4;                      // basis ring depth (single CTA: 4 x 24 KB)
+constexpr int kBStagesPair = 8;                   // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
 constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
 constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
 constexpr int kGroup = 32;                       // frames per group (one converter / epilogue warp)
@@ -78,7 +79,8 @@ struct Params {
 };
 
 struct __align__(8) Barriers {
-  uint64_t b_full[kBStages2], b_empty[kBStages2];
+  uint64_t b_full[kBStagesPair], b_empty[kBStagesPair];
+  uint64_t b_peer[kBStagesPair];                      // CTA pair: the peer CTA's half of the basis stage has landed
   uint64_t a_full[kAStages2], a_empty[kAStages2];
   uint64_t acc_full, acc_empty;
 };
@@ -128,17 +130,74 @@ __device__ __noinline__ void park_multi(uint32_t pa, float lo, float hi) {
   st_s(pa + 4, ld_s(pa + 4) + hi);
 }
 
+// ---- CTA-pair (cta_group::2) helpers
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t local_bar, uint32_t cta) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_bar), "r"(cta));
+  // default semantics (release at CTA scope), as CUTLASS ClusterBarrier::arrive: what is handed over lives in TMEM / was
+  // written by TMA and is ordered by the tcgen05 fences and the transaction barrier; a cluster-scope release would cost
+  // MEMBAR.ALL.GPU + CCTL.IVALL per arrive
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok;
+}
+// bounded wait with cluster-scope acquire (barriers the peer CTA arrives on)
+__device__ __noinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int32_t* status, int code) {
+  const long long t0 = clock64();
+  while (!mbar_try_wait_cluster(bar, parity)) {
+    if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
+  }
+}
+// D[tmem, both CTAs] (+)= A[tmem, both CTAs] * B[smem halves of both CTAs]^T, kind::tf32, M = 256, K = 8; leader CTA only
+__device__ __forceinline__ void mma_tf32_ts2(uint32_t d, uint32_t a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d), "r"(a), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+// completion of the pair's MMAs -> one arrival on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tc_commit2(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+
 }  // namespace f2
 
-template <bool kPower1, bool kDebug>
+// kPair: two CTAs of a cluster (the two SMs of a TPC) work on adjacent tiles with ONE tcgen05.mma.cta_group::2 stream:
+// M = 256 (128 rows per CTA, each CTA's A operand and accumulators in its own TMEM), and each CTA stages only HALF of
+// every basis stage (96 of the 192 bins) -- the tensor cores of both SMs read both halves.  Per SM that halves the
+// basis L2 -> smem traffic, the smem space of the basis ring and the B-operand smem reads.  CTA 0 issues the MMAs; the
+// peer's converters / epilogue arrive on CTA 0's barriers, tcgen05.commit multicasts to both CTAs' barriers.
+template <bool kPower1, bool kDebug, bool kPair>
 __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P) {
   using namespace f2;
+  constexpr int kBS = kPair ? kBStagesPair : kBStages2;    // basis ring depth
   extern __shared__ __align__(1024) uint8_t smem[];
   // ---- carve shared memory
   const int nb = P.nb;
-  const uint32_t b_stage_bytes = (uint32_t)nb * 128u;       // 4 arrays x 2 k-halves x nb rows x 16 B
+  const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
+  const int nbh = kPair ? nb / 2 : nb;                      // basis rows (bins) staged by this CTA
+  const uint32_t b_stage_bytes = (uint32_t)nbh * 128u;      // 4 arrays x 2 k-halves x nbh rows x 16 B
   uint8_t* s_b = smem;                                       // basis ring
-  uint8_t* s_raw = s_b + (size_t)kBStages2 * b_stage_bytes;   // raw audio ring
+  uint8_t* s_raw = s_b + (size_t)kBS * b_stage_bytes;   // raw audio ring
   float2* s_melw = reinterpret_cast<float2*>(s_raw + (size_t)kConvWarps2 * kDepth * kStageBytes);
   uint32_t* s_adv = reinterpret_cast<uint32_t*>(s_melw + P.nbt);                  // [nbt/16] single / multi close masks
   uint32_t* s_adv2 = s_adv + P.nbt / 16;                                           // [nbt/16] 2-bit close counts
@@ -159,25 +218,34 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   for (int i = threadIdx.x; i < P.n_mels; i += kThreads2) s_norm[i] = P.norms ? P.norms[i] : 1.0f;
   for (int i = threadIdx.x; i < kTileM * park_pitch; i += kThreads2) s_park[i] = 0.f;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kBStages2; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
-    for (int i = 0; i < kAStages2; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
+    for (int i = 0; i < kBS; ++i) {
+      mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); mbar_init(smem_u32(&bars->b_peer[i]), 1);
+    }
+    for (int i = 0; i < kAStages2; ++i) { mbar_init(smem_u32(&bars->a_full[i]), kPair ? 8 : 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
     mbar_init(smem_u32(&bars->acc_full), 1);
-    mbar_init(smem_u32(&bars->acc_empty), kEpiWarps);
+    mbar_init(smem_u32(&bars->acc_empty), kPair ? 2 * kEpiWarps : kEpiWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpTmem) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (kPair) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   // Programmatic dependent launch: everything above (plan constants, barriers, TMEM) overlaps k_prep, which produces
   // the frame counts, group prefix and edge buffers read below.
   asm volatile("griddepcontrol.wait;" ::: "memory");
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all(); else __syncthreads();       // pair: the peer's barriers must exist before anyone arrives on them
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
   const int64_t total_groups = P.group_off[P.B];
   const int num_tiles = (int)((total_groups + 3) / 4);
+  // a pair walks tiles (2j, 2j+1) in lock step: both CTAs run the same number of iterations, a missing odd tile is empty
+  auto tile_live = [&](int tile) { return (kPair ? (tile & ~1) : tile) < num_tiles; };
 
   const int wgroup = warp >> 2;                        // setmaxnreg works on warpgroups: misc | converters | epilogue
   if (wgroup == 0) {
@@ -186,35 +254,59 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     // ===== basis producer: one bulk copy per k-step stage =====
     if (lane == 0 && !(P.exp_flags & 2)) {
       uint32_t seq = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+      for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
         for (int ps = 0; ps < P.passes; ++ps)
           for (int ks = 0; ks < kKS; ++ks, ++seq) {
-            const uint32_t st = seq % kBStages2, use = seq / kBStages2;
+            const uint32_t st = seq % kBS, use = seq / kBS;
             mbar_wait<1>(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
             const uint32_t full = smem_u32(&bars->b_full[st]);
             mbar_expect_tx(full, b_stage_bytes);
             bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
-                     P.basis + ((size_t)ps * kKS + ks) * (b_stage_bytes / 4), b_stage_bytes, full);
+                     P.basis + (((size_t)ps * kKS + ks) * (kPair ? 2 : 1) + cta_rank) * (b_stage_bytes / 4), b_stage_bytes, full);
           }
     }
     __syncwarp();
   } else if (warp == kWarpMma) {
     // ===== MMA issuer: warp-uniform waits, one elected lane issues =====
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nb >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+    if (kPair && cta_rank != 0) {
+      // peer CTA: no MMAs to issue; tell the leader when my half of each basis stage has landed
+      if (lane == 0 && !(P.exp_flags & 2)) {
+        uint32_t seq = 0;
+        for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
+          for (int ps = 0; ps < P.passes; ++ps)
+            for (int ks = 0; ks < kKS; ++ks, ++seq) {
+              const uint32_t st = seq % kBS, use = seq / kBS;
+              mbar_wait<1>(smem_u32(&bars->b_full[st]), use & 1, P.status, 204);
+              mbar_arrive_cluster(smem_u32(&bars->b_peer[st]), 0);
+            }
+      }
+      __syncwarp();
+    } else {
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nb >> 3) << 17) |
+                           ((uint32_t)((kPair ? 2 * kTileM : kTileM) >> 4) << 24);
     const uint32_t desc_hi = (128u >> 4) | (1u << 14);          // SBO = 128 B, descriptor version 1
-    const uint32_t desc_lo0 = (((uint32_t)nb * 16u) >> 4) << 16;  // LBO = nb*16 B between the two k-halves
-    const uint32_t arr16 = ((uint32_t)nb * 32u) >> 4;           // one operand array, in 16 B units
+    const uint32_t desc_lo0 = (((uint32_t)nbh * 16u) >> 4) << 16;  // LBO = nbh*16 B between the two k-halves
+    const uint32_t arr16 = ((uint32_t)nbh * 32u) >> 4;          // one operand array, in 16 B units
     const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
     const uint32_t d_re = tmem, d_im = tmem + kNBMax;
     uint32_t kseq = 0, pseq = 0;
     uint32_t as = 0, ause = 0;                                   // A stage = kseq % kAStages2, its use count
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x)
+    for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        if (!(P.exp_flags & 4)) mbar_wait<1>(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        if (!(P.exp_flags & 4)) {
+          if (kPair) { if (!mbar_try_wait_cluster(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1)) mbar_wait_cluster(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201); }
+          else mbar_wait<1>(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
+        }
         for (int ks = 0; ks < kKS; ++ks, ++kseq) {
-          const uint32_t st = kseq % kBStages2, use = kseq / kBStages2;
-          if (!(P.exp_flags & 1)) mbar_wait<1>(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
-          if (!(P.exp_flags & 2)) mbar_wait<1>(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+          const uint32_t st = kseq % kBS, use = kseq / kBS;
+          if (!(P.exp_flags & 1)) {
+            if (kPair) { if (!mbar_try_wait_cluster(smem_u32(&bars->a_full[as]), ause & 1)) mbar_wait_cluster(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202); }
+            else mbar_wait<1>(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+          }
+          if (!(P.exp_flags & 2)) {
+            mbar_wait<1>(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+            if (kPair && !mbar_try_wait_cluster(smem_u32(&bars->b_peer[st]), use & 1)) mbar_wait_cluster(smem_u32(&bars->b_peer[st]), use & 1, P.status, 205);
+          }
           tc_fence_after();
           if (elect_one_sync()) {
             const uint32_t a_base = tmem + kColA2 + as * 32;
@@ -225,24 +317,29 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             const uint64_t s_lo = ((uint64_t)desc_hi << 32) | (lo + 3 * arr16);
             const uint32_t e_hi = a_base, e_lo = a_base + 8, o_hi = a_base + 16, o_lo = a_base + 24;
             const uint32_t first = ks == 0 ? 0u : 1u;
+            auto mma = [&](uint32_t d, uint32_t a, uint64_t b, uint32_t acc) {
+              if (kPair) mma_tf32_ts2(d, a, b, idesc, acc); else mma_tf32_ts(d, a, b, idesc, acc);
+            };
+            auto commit = [&](uint32_t bar) { if (kPair) tc_commit2(bar); else tc_commit(bar); };
             if (!(P.exp_flags & 32)) {
-              mma_tf32_ts(d_re, e_lo, c_hi, idesc, first);   // small terms first
-              mma_tf32_ts(d_re, e_hi, c_lo, idesc, 1u);
-              mma_tf32_ts(d_re, e_hi, c_hi, idesc, 1u);
+              mma(d_re, e_lo, c_hi, first);                  // small terms first
+              mma(d_re, e_hi, c_lo, 1u);
+              mma(d_re, e_hi, c_hi, 1u);
               if (ks < kKS - 1) {                            // the centre-tap k-step has no sine part
-                mma_tf32_ts(d_im, o_lo, s_hi, idesc, first);
-                mma_tf32_ts(d_im, o_hi, s_lo, idesc, 1u);
-                mma_tf32_ts(d_im, o_hi, s_hi, idesc, 1u);
+                mma(d_im, o_lo, s_hi, first);
+                mma(d_im, o_hi, s_lo, 1u);
+                mma(d_im, o_hi, s_hi, 1u);
               }
             }
-            tc_commit(smem_u32(&bars->b_empty[st]));         // basis stage free once these MMAs retire
-            tc_commit(smem_u32(&bars->a_empty[as]));         // A stage free
-            if (ks == kKS - 1) tc_commit(smem_u32(&bars->acc_full));
+            commit(smem_u32(&bars->b_empty[st]));            // basis stage free once these MMAs retire
+            commit(smem_u32(&bars->a_empty[as]));            // A stage free
+            if (ks == kKS - 1) commit(smem_u32(&bars->acc_full));
           }
           __syncwarp();
           if (++as == kAStages2) { as = 0; ++ause; }
         }
       }
+    }
   }
   } else if (wgroup <= kSets) {
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsConv));
@@ -335,7 +432,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");   // empty groups keep the wait_group count uniform
-      if (ic.tile < num_tiles && advance(ic)) load_tile(ic.tile);
+      if (tile_live(ic.tile) && advance(ic)) load_tile(ic.tile);
     };
 
     load_tile(ic.tile);
@@ -345,7 +442,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 
     Cursor cc{(int)blockIdx.x, 0, set};
     uint32_t mine = 0, kseq = set;                     // kseq: sequence number of my current k-step (A stage = kseq % 4)
-    while (cc.tile < num_tiles) {
+    while (tile_live(cc.tile)) {
       const uint32_t stage = mine % kDepth;
       asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
       __syncwarp();
@@ -407,7 +504,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
+      if (lane == 0) { if (kPair) mbar_arrive_cluster(smem_u32(&bars->a_full[as]), 0); else mbar_arrive(smem_u32(&bars->a_full[as])); }
       ++mine;
       kseq += kSets;
       if (advance(cc)) xc = xc_next;
@@ -427,7 +524,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
     const uint32_t bar_done = 1 + q, bar_flushed = 5 + q, bar_clean = 9 + q;   // named barriers of this quarter's four warps
     uint32_t pseq = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x) {
       // Sparse mel contraction.  Every bin feeds the running pair of adjacent filters (cur, cur+1) of its chain; the host
       // table says how many filters close before each bin (bit j: one, predicated inline; bit 16+j: two or three, rare,
       // out of line).  A closed filter's partial sum is added to its parked sum (`old`, prefetched one close ahead; the
@@ -451,7 +548,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             if (r16 + 16 >= cb && qr == 3) {           // my accumulator columns are in registers: hand them back
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty));
+              if (lane == 0) { if (kPair) mbar_arrive_cluster(smem_u32(&bars->acc_empty), 0); else mbar_arrive(smem_u32(&bars->acc_empty)); }
             }
             if (kDebug) {
               const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
@@ -565,9 +662,10 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 
   // ---- teardown
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all(); else __syncthreads();       // pair: the leader's MMAs read the peer's TMEM and smem
   if (warp == kWarpTmem) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTmemCols) : "memory");
+    if (kPair) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTmemCols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTmemCols) : "memory");
   }
 }

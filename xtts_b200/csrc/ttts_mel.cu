@@ -131,6 +131,8 @@ struct ttts_mel_plan {
   float2* d_melw2 = nullptr;   // [nbt2]
   uint32_t* d_meladv2 = nullptr;  // [nbt2/16], 2 bits per bin
   float* d_win2 = nullptr;     // [512]
+  int pair = 0;                // 1: CTA pairs (cta_group::2), each CTA stages half of every basis stage (TTTS_MEL_PAIR=0 disables)
+  float* d_basis2p = nullptr;  // [2 sp][33][2 halves][4 arrays][2 k-halves][nb2/2][4]: the per-CTA half stages
 };
 
 // ------------------------------------------------------------------------------------------
@@ -347,6 +349,22 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
     }
   }
 
+  p->pair = p->nb2 % 32 == 0;                 // CTA pairs by default (TTTS_MEL_PAIR=0: one CTA per tile stream)
+  if (const char* e3 = getenv("TTTS_MEL_PAIR")) p->pair = p->pair && atoi(e3) != 0;
+  std::vector<float> img2p;
+  if (p->pair) {                              // same values, each stage split into the two CTAs' bin halves
+    const int nh = nb2 / 2;
+    img2p.resize(img2.size());
+    for (size_t stg = 0; stg < (size_t)2 * p->sp * 33; ++stg)
+      for (int half = 0; half < 2; ++half)
+        for (int arr = 0; arr < 4; ++arr)
+          for (int j = 0; j < 2; ++j)
+            for (int r = 0; r < nh; ++r)
+              for (int e4 = 0; e4 < 4; ++e4)
+                img2p[stg * stage2_floats + ((((size_t)half * 4 + arr) * 2 + j) * nh + r) * 4 + e4] =
+                    img2[stg * stage2_floats + (((size_t)arr * 2 + j) * nb2 + half * nh + r) * 4 + e4];
+  }
+
   cudaError_t e;
   int dev = 0;
   e = cudaGetDevice(&dev);
@@ -367,6 +385,7 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   up((void**)&p->d_melw2, melw2.data(), melw2.size() * sizeof(float2));
   up((void**)&p->d_meladv2, meladv2.data(), meladv2.size() * sizeof(uint32_t));
   up((void**)&p->d_win2, win2.data(), win2.size() * 4);
+  if (p->pair) up((void**)&p->d_basis2p, img2p.data(), img2p.size() * 4);
   if (e != cudaSuccess) {
     int rc = fail(TTTS_MEL_ECUDA, "plan upload: %s", cudaGetErrorString(e));
     ttts_mel_plan_destroy(p);
@@ -392,7 +411,7 @@ extern "C" void ttts_mel_plan_destroy(ttts_mel_plan* p) {
   if (!p) return;
   cudaFree(p->d_basis); cudaFree(p->d_melw); cudaFree(p->d_meladv); cudaFree(p->d_norms);
   cudaFree(p->d_cosf); cudaFree(p->d_sinf); cudaFree(p->d_fb);
-  cudaFree(p->d_basis2); cudaFree(p->d_melw2); cudaFree(p->d_meladv2); cudaFree(p->d_win2);
+  cudaFree(p->d_basis2); cudaFree(p->d_melw2); cudaFree(p->d_meladv2); cudaFree(p->d_win2); cudaFree(p->d_basis2p);
   delete p;
 }
 
@@ -1230,7 +1249,7 @@ size_t logmel_smem_bytes(const ttts_mel_plan* p) {
 }
 
 size_t logmel2_smem_bytes(const ttts_mel_plan* p) {
-  size_t s = (size_t)f2::kBStages2 * p->nb2 * 128 + (size_t)f2::kConvWarps2 * f2::kDepth * f2::kStageBytes +
+  size_t s = (size_t)(p->pair ? f2::kBStagesPair * (p->nb2 / 2) : f2::kBStages2 * p->nb2) * 128 + (size_t)f2::kConvWarps2 * f2::kDepth * f2::kStageBytes +
              (size_t)p->nbt2 * sizeof(float2) + (size_t)(2 * (p->nbt2 / 16) + 4) * 4 + 512 * 4 + kMaxMels * 4 +
              (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + (size_t)2 * f2::kChains * 2 * kTileM * 4 + sizeof(f2::Barriers) + 16;
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
@@ -1286,20 +1305,26 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.exp_flags = g_exp_flags;
     const size_t smem = logmel2_smem_bytes(p);
     const bool pw1 = p->cfg.power == 1.0f;
+    const bool pair = p->pair && !dbg_reim && p->num_sms >= 2;
+    if (pair) P.basis = p->d_basis2p;
     void (*kern)(const f2::Params) =
-        dbg_reim ? (pw1 ? k_logmel2<true, true> : k_logmel2<false, true>)
-                 : (pw1 ? k_logmel2<true, false> : k_logmel2<false, false>);
+        dbg_reim ? (pw1 ? k_logmel2<true, true, false> : k_logmel2<false, true, false>)
+        : pair   ? (pw1 ? k_logmel2<true, false, true> : k_logmel2<false, false, true>)
+                 : (pw1 ? k_logmel2<true, false, false> : k_logmel2<false, false, false>);
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
     if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
     {
       // programmatic dependent launch behind k_prep: the prologue of the persistent kernel overlaps it
       cudaLaunchConfig_t lc{};
-      lc.gridDim = dim3((unsigned)p->num_sms); lc.blockDim = dim3(f2::kThreads2); lc.dynamicSmemBytes = smem; lc.stream = stream;
-      cudaLaunchAttribute at[1];
+      lc.gridDim = dim3((unsigned)(pair ? p->num_sms & ~1 : p->num_sms)); lc.blockDim = dim3(f2::kThreads2);
+      lc.dynamicSmemBytes = smem; lc.stream = stream;
+      cudaLaunchAttribute at[2];
       at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
       at[0].val.programmaticStreamSerializationAllowed = 1;
-      lc.attrs = at; lc.numAttrs = 1;
+      at[1].id = cudaLaunchAttributeClusterDimension;           // CTA pair = the two SMs of a TPC
+      at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+      lc.attrs = at; lc.numAttrs = pair ? 2 : 1;
       CUDA_TRY(cudaLaunchKernelEx(&lc, kern, P));
     }
     if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
