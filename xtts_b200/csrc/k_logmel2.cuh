@@ -46,6 +46,10 @@ constexpr int kBStages2 = 4;                      // basis ring depth (single CT
 constexpr int kBStagesPair = 8;                   // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
 constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
 constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
+#ifndef F2_QR_UNROLL
+#define F2_QR_UNROLL 1
+#endif
+constexpr int kQrUnroll = F2_QR_UNROLL;          // unrolling of the epilogue's 4-bin rounds
 constexpr int kGroup = 32;                       // frames per group (one converter / epilogue warp)
 
 struct Params {
@@ -539,8 +543,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         tc_fence_after();
         for (int r16 = 0; r16 < cb; r16 += 16) {
           const uint32_t advw = s_adv[(bin_base + r16) >> 4];
-#pragma unroll 1
-          for (int qr = 0; qr < 4; ++qr) {             // not unrolled: the scan stays resident in the instruction cache
+#pragma unroll(kQrUnroll)
+          for (int qr = 0; qr < 4; ++qr) {             // barely unrolled: the scan stays resident in the instruction cache
             uint32_t re[4], im[4];
             tmem_ld4(t_re + r16 + 4 * qr, re);
             tmem_ld4(t_im + r16 + 4 * qr, im);
