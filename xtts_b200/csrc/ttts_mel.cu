@@ -2,21 +2,23 @@
 //
 // Replaces, for the path TorchMelSpectrogram.forward (ttts/utils/utils.py:509-522) takes through
 // torchaudio/torch.stft/matmul, the whole chain reflect-pad -> frame -> Hann -> rDFT -> |.|^p ->
-// mel filterbank -> log(clamp) -> / mel_norms with five kernels:
+// mel filterbank -> log(clamp) -> / mel_norms with these kernels:
 //
 //   k_prep    block 0: lengths -> n_frames (torch.stft frame count) + exclusive prefix (frame -> clip map);
 //             blocks 1..B: per-clip edge buffers (the few frames that touch the reflect padding), zeros for padded
 //             output frames, padding mask
 //   k_pad     full per-clip reflect padding into the workspace (only for inputs that are not 16 B addressable)
-//   k_logmel  the fused hot kernel (persistent, warp-specialised, one CTA per SM):
-//               loader warp     cp.async 16 B gathers of the overlapping hop windows -> smem ring
-//               converter warps even/odd fold  E[n]=f[n]+f[N-n], O[n]=f[n]-f[N-n]  (halves K),
-//                               TF32 hi/lo split, tcgen05.st into TMEM (A operand never in smem)
+//   k_logmel2 the fused hot kernel (k_logmel2.cuh; default): persistent, warp-specialised, CTA pairs (cta_group::2),
+//             double-folded DFT-GEMM (K = 256 + centre tap, even / odd bin passes), 3xTF32, A operand in TMEM,
+//             16 epilogue warps; spectrum magnitudes never leave the SM
+//   k_logmel  the first-generation fused kernel (single fold, K = 512), kept as a second tcgen05 implementation
+//             (TTTS_MEL_ALGO=1):
+//               converter warps cp.async 16 B gathers of the overlapping hop windows, even/odd fold
+//                               E[n]=f[n]+f[N-n], O[n]=f[n]-f[N-n]  (halves K), TF32 hi/lo split, tcgen05.st into TMEM
 //               TMA warp        cp.async.bulk of pre-tiled windowed cos/sin basis stages -> smem ring
-//               MMA thread      tcgen05.mma kind::tf32, A from TMEM, B from smem, fp32 accumulators in
+//               MMA warp        tcgen05.mma kind::tf32, A from TMEM, B from smem, fp32 accumulators in
 //                               TMEM; 3-term error-compensated product hi*hi + lo*hi + hi*lo
 //               epilogue warps  tcgen05.ld -> re^2+im^2 -> sparse mel contraction -> log(clamp) -> /norm
-//             spectrum magnitudes never leave the SM.
 //   k_simt    the same maths on CUDA cores in plain fp32 (independent cross-check, not a fallback)
 //   k_stats   per-channel sum / sum-of-squares / count of log-mel for mel_norms
 //
