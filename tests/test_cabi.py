@@ -1,4 +1,4 @@
-"""The C-ABI library builds for sm_100a, loads, and exports every symbol include/ttts_mel.h declares.
+"""The C-ABI library builds for sm_100a, loads, and exports every symbol include/*.h declares.
 No compute calls here (no GPU in this container)."""
 import ctypes
 import os
@@ -12,14 +12,17 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _header_symbols():
-    src = open(os.path.join(ROOT, "include", "ttts_mel.h")).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(ttts_mel_[a-z0-9_]+)\s*\(", src)))
+    names = set()
+    for h in ("ttts_mel.h", "ttts_ingest.h"):
+        src = open(os.path.join(ROOT, "include", h)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names |= set(re.findall(r"\b(ttts_[a-z0-9_]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_library_exports_every_declared_symbol(built_lib):
     names = _header_symbols()
-    assert len(names) >= 18
+    assert len(names) >= 23
     for n in names:
         assert getattr(built_lib, n) is not None, n
     from xtts_b200 import _cabi

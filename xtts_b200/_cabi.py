@@ -1,4 +1,4 @@
-"""ctypes binding of the C ABI in ``include/ttts_mel.h`` (``libttts_mel.so``, built in-tree).
+"""ctypes binding of the C ABI in ``include/ttts_mel.h`` and ``include/ttts_ingest.h`` (``libttts_mel.so``, built in-tree).
 
 There is no CPU implementation behind this module: if the shared library is missing or a call
 fails, an exception is raised.
@@ -48,6 +48,15 @@ SYMBOLS = {
     "ttts_mel_set_experiment": (None, [c_int32]),
     "ttts_mel_profile_enable": (ctypes.c_int, [c_int32]),
     "ttts_mel_profile_collect": (ctypes.c_int, [c_void_p, c_int32]),
+    # include/ttts_ingest.h
+    "ttts_pcm16_to_f32": (ctypes.c_int, [c_void_p, c_int64, c_int32, c_void_p, c_int32, c_int64, c_void_p, c_int64, c_void_p]),
+    "ttts_resample_plan_create": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, POINTER(c_void_p)]),
+    "ttts_resample_plan_destroy": (None, [c_void_p]),
+    "ttts_resample_out_len": (c_int64, [c_void_p, c_int64]),
+    "ttts_resample_forward": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int64, c_void_p,
+                                             c_int64, c_int32, c_void_p]),
+    "ttts_resample_pcm16_forward": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_int32, c_int64,
+                                                   c_void_p, c_int64, c_int32, c_void_p]),
     "ttts_mel_last_error": (c_char_p, []),
     "ttts_mel_version": (c_char_p, []),
 }

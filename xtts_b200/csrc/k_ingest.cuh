@@ -1,0 +1,363 @@
+// k_ingest.cuh -- ingestion in front of the log-mel path (C ABI in include/ttts_ingest.h):
+//   k_pcm16      interleaved int16 PCM -> float32 channel 0 (x / 32768)        HBM-bound: 2 C + 4 bytes per frame
+//   k_decimate   integer-ratio (2:1, 3:1, 4:1) windowed-sinc FIR, one phase     HBM-bound: 4 (or 2 C) ORIG + 4 bytes per output
+//   k_resample   general polyphase windowed-sinc FIR (orig -> new)              FMA-bound: 2 (2 width + orig) flop per output
+// The two FIR kernels read float32 or (fused decode) interleaved int16 PCM.
+// Reference: load_audio (ttts/utils/utils.py:32-47), mel_extract.py:15-21.  Included at the end of ttts_mel.cu
+// (one shared library); uses its fail() / CUDA_TRY / g_launches.
+#pragma once
+
+namespace ingest {
+
+constexpr int kThreads = 256;
+constexpr float kPcmScale = 1.0f / 32768.0f;
+
+// sample s of a clip: float32 as is, int16 -> channel 0 of frame s, scaled
+__device__ __forceinline__ float load_sample(const float* src, long long s, int) { return __ldg(src + s); }
+__device__ __forceinline__ float load_sample(const int16_t* src, long long s, int channels) {
+  return (float)__ldg(src + s * channels) * kPcmScale;
+}
+
+// ---------------------------------------------------------------------------------------------- k_pcm16
+// One thread = 8 consecutive frames of one clip.  kC = 1: one 16-byte load; kC = 2: two; kC = 0: scalar loads.
+template <int kC>
+__global__ void __launch_bounds__(kThreads) k_pcm16(const int16_t* __restrict__ pcm, long long in_stride, int channels,
+                                                    const long long* __restrict__ frames_b, long long frames,
+                                                    float* __restrict__ out, long long out_stride, int vec_ok) {
+  const int b = blockIdx.y;
+  const long long nf = frames_b ? min(max(frames_b[b], 0LL), frames) : frames;
+  const int16_t* src = pcm + (long long)b * in_stride;
+  float* dst = out + (long long)b * out_stride;
+  for (long long f0 = 8LL * (blockIdx.x * (long long)kThreads + threadIdx.x); f0 < frames;
+       f0 += 8LL * kThreads * gridDim.x) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    if (f0 + 8 <= nf && vec_ok && kC == 1) {
+      const int4 s = __ldg(reinterpret_cast<const int4*>(src + f0));
+      const int w[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[2 * j] = (float)(short)(w[j] & 0xFFFF) * kPcmScale;
+        v[2 * j + 1] = (float)(short)(w[j] >> 16) * kPcmScale;
+      }
+    } else if (f0 + 8 <= nf && vec_ok && kC == 2) {
+      const int4 s0 = __ldg(reinterpret_cast<const int4*>(src + 2 * f0));       // 4 frames x (ch0, ch1)
+      const int4 s1 = __ldg(reinterpret_cast<const int4*>(src + 2 * f0 + 8));
+      const int w[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = (float)(short)(w[j] & 0xFFFF) * kPcmScale;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (f0 + j < nf) v[j] = (float)src[(f0 + j) * channels] * kPcmScale;
+    }
+    if (f0 + 8 <= frames && vec_ok) {
+      reinterpret_cast<float4*>(dst + f0)[0] = make_float4(v[0], v[1], v[2], v[3]);
+      reinterpret_cast<float4*>(dst + f0)[1] = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (f0 + j < frames) dst[f0 + j] = v[j];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- k_decimate
+struct TapsParam { float t[64]; };     // by value: the FMAs read the taps straight from the constant bank
+
+constexpr int kDecR = 8;               // consecutive outputs per thread
+constexpr int kDecTile = kThreads * kDecR;
+// shared-memory index with 4 floats of padding per 16: a thread's window starts 8 ORIG floats after its
+// neighbour's, and the padding spreads the 16-byte chunks of 8 neighbouring lanes over distinct banks
+__device__ __forceinline__ int dec_pad(int i) { return i + ((i >> 4) << 2); }
+
+// new == 1: out[j] = sum_k xpad[j * ORIG + k] * taps[k].  One CTA = 2048 consecutive outputs of one clip: the
+// segment is staged once in shared memory, each thread pulls the (R - 1) ORIG + KW samples its 8 outputs share into
+// registers with 16-byte loads, and the R x KW FMAs take their taps from the kernel-parameter constant bank.
+template <int ORIG, int KW, typename TIn>
+__global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x, long long row_stride, int channels,
+                                                       const long long* __restrict__ lengths, long long L,
+                                                       const TapsParam taps, int width, float* __restrict__ out,
+                                                       long long out_stride, long long out_cols, int clip) {
+  constexpr int kWin = (kDecR - 1) * ORIG + KW;
+  constexpr int kWinQ = (kWin + 3) / 4;
+  constexpr int kSeg = (kThreads - 1) * kDecR * ORIG + kWinQ * 4;
+  __shared__ __align__(16) float xs[kSeg + (kSeg >> 4) * 4 + 4];
+  const int b = blockIdx.y;
+  const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
+  const long long olen = (len + ORIG - 1) / ORIG;
+  const long long j0 = (long long)blockIdx.x * kDecTile;
+  float* dst = out + (long long)b * out_stride;
+  const long long jend = min(j0 + kDecTile, out_cols);
+  if (j0 >= olen) {
+    for (long long j = j0 + threadIdx.x; j < jend; j += kThreads) dst[j] = 0.f;
+    return;
+  }
+  const TIn* src = x + (long long)b * row_stride;
+  const long long s0 = j0 * ORIG - width;
+  for (int i = threadIdx.x; i < kSeg; i += kThreads) {
+    const long long s = s0 + i;
+    xs[dec_pad(i)] = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+  }
+  __syncthreads();
+  float w[kWinQ * 4];
+  const int start = threadIdx.x * (kDecR * ORIG);
+#pragma unroll
+  for (int c = 0; c < kWinQ; ++c) {
+    const float4 v = *reinterpret_cast<const float4*>(&xs[dec_pad(start + 4 * c)]);
+    w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
+  }
+  float acc[kDecR];
+#pragma unroll
+  for (int r = 0; r < kDecR; ++r) acc[r] = 0.f;
+#pragma unroll
+  for (int k = 0; k < KW; ++k) {
+    const float t = taps.t[k];
+#pragma unroll
+    for (int r = 0; r < kDecR; ++r) acc[r] = fmaf(w[r * ORIG + k], t, acc[r]);
+  }
+  const long long j = j0 + (long long)threadIdx.x * kDecR;
+#pragma unroll
+  for (int r = 0; r < kDecR; ++r) {
+    float v = (j + r < olen) ? acc[r] : 0.f;
+    if (clip) v = fminf(fmaxf(v, -1.f), 1.f);
+    acc[r] = v;
+  }
+  if (j + kDecR <= out_cols && (out_stride & 3) == 0 && ((uintptr_t)out & 15) == 0) {
+    reinterpret_cast<float4*>(dst + j)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    reinterpret_cast<float4*>(dst + j)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  } else {
+#pragma unroll
+    for (int r = 0; r < kDecR; ++r)
+      if (j + r < out_cols) dst[j + r] = acc[r];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- k_resample
+constexpr int kRI = 4;                 // rows (input strides) per thread item
+constexpr int kRP = 4;                 // consecutive phases per thread item: one 16-byte tap load + kRI sample loads
+                                       // feed kRI * kRP FMAs
+constexpr int kMaxSmemFloats = 16 * 1024;   // staged input segment per CTA (64 KB)
+
+// One CTA = `rows` input strides of one clip = rows * new_f outputs.  The input segment
+// x[row0 * orig - width, (row0 + rows - 1) * orig + kw - width) is staged in shared memory (zeros outside the clip);
+// a thread item is (row slot g, phase quad q) and owns rows g, g + ng, g + 2 ng, g + 3 ng (interleaved, so that lanes
+// that differ in g are `orig` floats apart in shared memory) x phases 4 q .. 4 q + 3:
+//   acc[r][c] += xs[row_r * orig + k] * tapsT[k][4 q + c]      over the kw taps;
+// tapsT is phase-minor with the phase count padded to a multiple of 4 (zero taps), so lanes read it coalesced.
+template <typename TIn>
+__global__ void __launch_bounds__(kThreads) k_resample(const TIn* __restrict__ x, long long row_stride, int channels,
+                                                       const long long* __restrict__ lengths, long long L,
+                                                       const float* __restrict__ tapsT, int orig, int new_f, int new_pad,
+                                                       int width, int kw, int rows, float* __restrict__ out,
+                                                       long long out_stride, long long out_cols, int clip) {
+  extern __shared__ float xs[];
+  const int b = blockIdx.y;
+  const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
+  const long long olen = (len * new_f + orig - 1) / orig;          // ceil(new * len / orig)
+  const long long row0 = (long long)blockIdx.x * rows;
+  float* dst = out + (long long)b * out_stride;
+  const long long j0 = row0 * new_f;
+  if (j0 >= out_cols) return;
+  const long long jend = min(j0 + (long long)rows * new_f, out_cols);
+  if (j0 >= olen) {                                                // tile entirely past this clip: zero fill
+    for (long long j = j0 + threadIdx.x; j < jend; j += kThreads) dst[j] = 0.f;
+    return;
+  }
+  const TIn* src = x + (long long)b * row_stride;
+  const long long s0 = row0 * orig - width;
+  const int seg = (rows - 1) * orig + kw;
+  for (int i = threadIdx.x; i < seg; i += kThreads) {
+    const long long s = s0 + i;
+    xs[i] = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+  }
+  __syncthreads();
+  const int ng = rows / kRI;
+  const int nq = new_pad / kRP;
+  const int items = ng * nq;
+  for (int it = threadIdx.x; it < items; it += kThreads) {
+    const int g = it / nq, q = it - g * nq;
+    float acc[kRI][kRP];
+    const float* xr[kRI];
+#pragma unroll
+    for (int r = 0; r < kRI; ++r) {
+      xr[r] = xs + (g + r * ng) * orig;
+#pragma unroll
+      for (int c = 0; c < kRP; ++c) acc[r][c] = 0.f;
+    }
+    const float4* tp = reinterpret_cast<const float4*>(tapsT) + q;
+#pragma unroll 4
+    for (int k = 0; k < kw; ++k) {
+      const float4 t = __ldg(tp + (long long)k * nq);
+#pragma unroll
+      for (int r = 0; r < kRI; ++r) {
+        const float v = xr[r][k];
+        acc[r][0] = fmaf(v, t.x, acc[r][0]);
+        acc[r][1] = fmaf(v, t.y, acc[r][1]);
+        acc[r][2] = fmaf(v, t.z, acc[r][2]);
+        acc[r][3] = fmaf(v, t.w, acc[r][3]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < kRI; ++r) {
+      const long long jr = (row0 + g + r * ng) * new_f;
+#pragma unroll
+      for (int c = 0; c < kRP; ++c) {
+        const int p = q * kRP + c;
+        const long long j = jr + p;
+        if (p < new_f && j < out_cols) {
+          float v = j < olen ? acc[r][c] : 0.f;
+          if (clip) v = fminf(fmaxf(v, -1.f), 1.f);
+          dst[j] = v;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace ingest
+
+// ------------------------------------------------------------------------------------------------ host / C ABI
+
+struct ttts_resample_plan {
+  int orig = 0, new_f = 0, new_pad = 0, width = 0, kw = 0;
+  int rows = 0;               // k_resample: input strides per CTA (multiple of ingest::kRI)
+  int decimate = 0;           // k_decimate<orig, kw> applies (new == 1, orig in 2..4, torchaudio's default width)
+  int device = 0;
+  float* d_tapsT = nullptr;   // [kw][new_pad], phases zero-padded to a multiple of 4
+  ingest::TapsParam taps1;    // the single phase of a decimator
+};
+
+extern "C" int ttts_pcm16_to_f32(const int16_t* pcm, int64_t in_stride, int32_t channels, const int64_t* frames_b,
+                                 int32_t B, int64_t frames, float* out, int64_t out_stride, void* stream) {
+  if (!pcm || !out) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || frames <= 0 || channels <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d frames=%lld channels=%d)", B, (long long)frames, channels);
+  if (in_stride < frames * channels) return fail(TTTS_MEL_EINVAL, "in_row_stride %lld < frames * channels", (long long)in_stride);
+  if (out_stride < frames) return fail(TTTS_MEL_EINVAL, "out_row_stride %lld < frames %lld", (long long)out_stride, (long long)frames);
+  if (B > 65535) return fail(TTTS_MEL_EINVAL, "B %d > 65535: split the batch", B);
+  const int vec_ok = (in_stride % 8 == 0) && (out_stride % 4 == 0) && ((uintptr_t)pcm % 16 == 0) && ((uintptr_t)out % 16 == 0);
+  const long long octs = (frames + 7) / 8;
+  long long gx = (octs + ingest::kThreads - 1) / ingest::kThreads;
+  if (gx > 148 * 16) gx = 148 * 16;
+  dim3 grid((unsigned)gx, (unsigned)B);
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long* fb = (const long long*)frames_b;
+  if (channels == 1) ingest::k_pcm16<1><<<grid, ingest::kThreads, 0, st>>>(pcm, in_stride, channels, fb, frames, out, out_stride, vec_ok);
+  else if (channels == 2) ingest::k_pcm16<2><<<grid, ingest::kThreads, 0, st>>>(pcm, in_stride, channels, fb, frames, out, out_stride, vec_ok);
+  else ingest::k_pcm16<0><<<grid, ingest::kThreads, 0, st>>>(pcm, in_stride, channels, fb, frames, out, out_stride, 0);
+  CUDA_TRY(cudaGetLastError());
+  g_launches = 1;
+  return 0;
+}
+
+extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_t new_f, int32_t width,
+                                         ttts_resample_plan** out) {
+  if (!taps || !out) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (orig < 1 || new_f < 1 || width < 1) return fail(TTTS_MEL_EINVAL, "bad resample geometry %d -> %d, width %d", orig, new_f, width);
+  const int kw = 2 * width + orig;
+  const int new_pad = (new_f + ingest::kRP - 1) / ingest::kRP * ingest::kRP;
+  // rows per CTA (k_resample): the staged segment bounds it; among the candidates take the one whose item count
+  // (rows / 4 x phase quads) wastes the fewest of the 256 threads' slots, preferring >= 4096 outputs per tile
+  const long long max_ng = ((ingest::kMaxSmemFloats - kw) / orig + 1) / ingest::kRI;
+  if (max_ng < 1) return fail(TTTS_MEL_EINVAL, "resample %d -> %d: stride too long for the staged segment", orig, new_f);
+  const int nq = new_pad / ingest::kRP;
+  long long want_ng = (4096 / new_f + ingest::kRI - 1) / ingest::kRI;
+  if (want_ng < 8) want_ng = 8;
+  if (want_ng > max_ng) want_ng = max_ng;
+  long long best_ng = want_ng;
+  double best_eff = 0.0;
+  for (long long ng = want_ng; ng <= max_ng && ng <= want_ng * 2; ++ng) {
+    const long long items = ng * nq, slots = (items + ingest::kThreads - 1) / ingest::kThreads * ingest::kThreads;
+    const double eff = (double)items / (double)slots;
+    if (eff > best_eff + 1e-9) { best_eff = eff; best_ng = ng; }
+  }
+  auto* p = new (std::nothrow) ttts_resample_plan();
+  if (!p) return fail(TTTS_MEL_ENOMEM, "host allocation failed");
+  p->orig = orig; p->new_f = new_f; p->new_pad = new_pad; p->width = width; p->kw = kw;
+  p->rows = (int)(best_ng * ingest::kRI);
+  p->decimate = (new_f == 1 && ((orig == 2 && kw == 28) || (orig == 3 && kw == 41) || (orig == 4 && kw == 54))) ? 1 : 0;
+  if (getenv("TTTS_RESAMPLE_GENERIC")) p->decimate = 0;
+  memset(&p->taps1, 0, sizeof(p->taps1));
+  if (p->decimate) memcpy(p->taps1.t, taps, kw * sizeof(float));
+  std::vector<float> t((size_t)kw * new_pad, 0.f);
+  for (int ph = 0; ph < new_f; ++ph)
+    for (int k = 0; k < kw; ++k) t[(size_t)k * new_pad + ph] = taps[(size_t)ph * kw + k];
+  cudaError_t e = cudaGetDevice(&p->device);
+  if (e == cudaSuccess) e = cudaMalloc(&p->d_tapsT, t.size() * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemcpy(p->d_tapsT, t.data(), t.size() * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(ingest::k_resample<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, ingest::kMaxSmemFloats * 4);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(ingest::k_resample<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, ingest::kMaxSmemFloats * 4);
+  if (e != cudaSuccess) {
+    int rc = fail(TTTS_MEL_ECUDA, "resample plan: %s", cudaGetErrorString(e));
+    ttts_resample_plan_destroy(p);
+    return rc;
+  }
+  *out = p;
+  return 0;
+}
+
+extern "C" void ttts_resample_plan_destroy(ttts_resample_plan* p) {
+  if (!p) return;
+  cudaFree(p->d_tapsT);
+  delete p;
+}
+
+extern "C" int64_t ttts_resample_out_len(const ttts_resample_plan* p, int64_t length) {
+  if (!p || length < 0) return fail(TTTS_MEL_EINVAL, "null plan or negative length");
+  return (length * p->new_f + p->orig - 1) / p->orig;
+}
+
+namespace {
+
+template <typename TIn>
+int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_stride, int channels, const int64_t* lengths,
+                    int32_t B, int64_t L, float* out, int64_t out_stride, int32_t clip, void* stream) {
+  if (!p || !x || !out) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || L <= 0 || channels <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d L=%lld channels=%d)", B, (long long)L, channels);
+  if (B > 65535) return fail(TTTS_MEL_EINVAL, "B %d > 65535: split the batch", B);
+  if (row_stride < L * channels) return fail(TTTS_MEL_EINVAL, "row_stride %lld < L %lld x channels %d", (long long)row_stride, (long long)L, channels);
+  const long long out_cols = ttts_resample_out_len(p, L);
+  if (out_stride < out_cols) return fail(TTTS_MEL_EINVAL, "out_row_stride %lld < %lld output samples", (long long)out_stride, out_cols);
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long* len = (const long long*)lengths;
+  if (p->decimate) {
+    const long long gx = (out_cols + ingest::kDecTile - 1) / ingest::kDecTile;
+    if (gx > 0x7FFFFFFFLL) return fail(TTTS_MEL_EINVAL, "clip too long");
+    dim3 grid((unsigned)gx, (unsigned)B);
+#define TTTS_DEC(O, K) ingest::k_decimate<O, K, TIn><<<grid, ingest::kThreads, 0, st>>>( \
+        x, row_stride, channels, len, L, p->taps1, p->width, out, out_stride, out_cols, clip)
+    if (p->orig == 2) TTTS_DEC(2, 28);
+    else if (p->orig == 3) TTTS_DEC(3, 41);
+    else TTTS_DEC(4, 54);
+#undef TTTS_DEC
+  } else {
+    const long long tile = (long long)p->rows * p->new_f;
+    const long long gx = (out_cols + tile - 1) / tile;
+    if (gx > 0x7FFFFFFFLL) return fail(TTTS_MEL_EINVAL, "clip too long");
+    const size_t smem = ((size_t)(p->rows - 1) * p->orig + p->kw) * sizeof(float);
+    dim3 grid((unsigned)gx, (unsigned)B);
+    ingest::k_resample<TIn><<<grid, ingest::kThreads, smem, st>>>(
+        x, row_stride, channels, len, L, p->d_tapsT, p->orig, p->new_f, p->new_pad, p->width, p->kw, p->rows, out,
+        out_stride, out_cols, clip);
+  }
+  CUDA_TRY(cudaGetLastError());
+  g_launches = 1;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int ttts_resample_forward(const ttts_resample_plan* p, const float* x, int64_t row_stride,
+                                     const int64_t* lengths, int32_t B, int64_t L, float* out, int64_t out_stride,
+                                     int32_t clip, void* stream) {
+  return resample_launch<float>(p, x, row_stride, 1, lengths, B, L, out, out_stride, clip, stream);
+}
+
+extern "C" int ttts_resample_pcm16_forward(const ttts_resample_plan* p, const int16_t* pcm, int64_t in_row_stride,
+                                           int32_t channels, const int64_t* frames, int32_t B, int64_t F, float* out,
+                                           int64_t out_stride, int32_t clip, void* stream) {
+  return resample_launch<int16_t>(p, pcm, in_row_stride, channels, frames, B, F, out, out_stride, clip, stream);
+}

@@ -24,6 +24,7 @@
 //
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
 #include "ttts_mel.h"
+#include "ttts_ingest.h"
 
 #include <cuda_runtime.h>
 
@@ -32,6 +33,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <type_traits>
 #include <vector>
 
@@ -1450,3 +1452,8 @@ extern "C" int ttts_mel_profile_collect(float* ms_out, int32_t capacity) {
 }
 
 extern "C" void ttts_mel_set_experiment(int32_t flags) { g_exp_flags = flags; }
+
+// ------------------------------------------------------------------------------------------
+// ingestion in front of the path (int16 PCM -> float32, sinc resample): include/ttts_ingest.h
+// ------------------------------------------------------------------------------------------
+#include "k_ingest.cuh"
