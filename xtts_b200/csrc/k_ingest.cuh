@@ -72,17 +72,41 @@ constexpr int kDecTile = kThreads * kDecR;
 // neighbour's, and the padding spreads the 16-byte chunks of 8 neighbouring lanes over distinct banks
 __device__ __forceinline__ int dec_pad(int i) { return i + ((i >> 4) << 2); }
 
+// four consecutive samples s .. s+3 (s % 4 == 0, all inside the clip, row base suitably aligned: `vec`)
+__device__ __forceinline__ float4 load_quad(const float* src, long long s, int, int vec) {
+  if (vec) return __ldg(reinterpret_cast<const float4*>(src + s));
+  return make_float4(__ldg(src + s), __ldg(src + s + 1), __ldg(src + s + 2), __ldg(src + s + 3));
+}
+__device__ __forceinline__ float4 load_quad(const int16_t* src, long long s, int channels, int vec) {
+  if (vec && channels == 1) {
+    const int2 w = __ldg(reinterpret_cast<const int2*>(src + s));
+    return make_float4((float)(short)(w.x & 0xFFFF) * kPcmScale, (float)(short)(w.x >> 16) * kPcmScale,
+                       (float)(short)(w.y & 0xFFFF) * kPcmScale, (float)(short)(w.y >> 16) * kPcmScale);
+  }
+  if (vec && channels == 2) {
+    const int4 w = __ldg(reinterpret_cast<const int4*>(src + 2 * s));
+    return make_float4((float)(short)(w.x & 0xFFFF) * kPcmScale, (float)(short)(w.y & 0xFFFF) * kPcmScale,
+                       (float)(short)(w.z & 0xFFFF) * kPcmScale, (float)(short)(w.w & 0xFFFF) * kPcmScale);
+  }
+  return make_float4(load_sample(src, s, channels), load_sample(src, s + 1, channels),
+                     load_sample(src, s + 2, channels), load_sample(src, s + 3, channels));
+}
+
 // new == 1: out[j] = sum_k xpad[j * ORIG + k] * taps[k].  One CTA = 2048 consecutive outputs of one clip: the
-// segment is staged once in shared memory, each thread pulls the (R - 1) ORIG + KW samples its 8 outputs share into
+// segment is staged once in shared memory (16-byte loads and stores: it starts at the multiple of 4 at or below
+// the first sample the tile needs, kOff samples early), each thread pulls the samples its 8 outputs share into
 // registers with 16-byte loads, and the R x KW FMAs take their taps from the kernel-parameter constant bank.
 template <int ORIG, int KW, typename TIn>
 __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x, long long row_stride, int channels,
                                                        const long long* __restrict__ lengths, long long L,
-                                                       const TapsParam taps, int width, float* __restrict__ out,
-                                                       long long out_stride, long long out_cols, int clip) {
-  constexpr int kWin = (kDecR - 1) * ORIG + KW;
+                                                       const TapsParam taps, float* __restrict__ out,
+                                                       long long out_stride, long long out_cols, int clip, int vec) {
+  constexpr int kWidth = (KW - ORIG) / 2;
+  constexpr int kOff = (4 - (kWidth & 3)) & 3;
+  constexpr int kWin = kOff + (kDecR - 1) * ORIG + KW;
   constexpr int kWinQ = (kWin + 3) / 4;
   constexpr int kSeg = (kThreads - 1) * kDecR * ORIG + kWinQ * 4;
+  static_assert((kDecTile * ORIG) % 4 == 0 && kSeg % 4 == 0, "tile origin must stay 4-aligned");
   __shared__ __align__(16) float xs[kSeg + (kSeg >> 4) * 4 + 4];
   const int b = blockIdx.y;
   const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
@@ -95,10 +119,19 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
     return;
   }
   const TIn* src = x + (long long)b * row_stride;
-  const long long s0 = j0 * ORIG - width;
-  for (int i = threadIdx.x; i < kSeg; i += kThreads) {
-    const long long s = s0 + i;
-    xs[dec_pad(i)] = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+  const long long s0 = j0 * ORIG - kWidth - kOff;          // multiple of 4 (negative for the first tile)
+  for (int q = threadIdx.x; q < kSeg / 4; q += kThreads) {
+    const long long s = s0 + 4 * q;
+    float4 v;
+    if (s >= 0 && s + 4 <= len) {
+      v = load_quad(src, s, channels, vec);
+    } else {
+      v.x = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+      v.y = (s + 1 >= 0 && s + 1 < len) ? load_sample(src, s + 1, channels) : 0.f;
+      v.z = (s + 2 >= 0 && s + 2 < len) ? load_sample(src, s + 2, channels) : 0.f;
+      v.w = (s + 3 >= 0 && s + 3 < len) ? load_sample(src, s + 3, channels) : 0.f;
+    }
+    *reinterpret_cast<float4*>(&xs[dec_pad(4 * q)]) = v;
   }
   __syncthreads();
   float w[kWinQ * 4];
@@ -115,7 +148,7 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
   for (int k = 0; k < KW; ++k) {
     const float t = taps.t[k];
 #pragma unroll
-    for (int r = 0; r < kDecR; ++r) acc[r] = fmaf(w[r * ORIG + k], t, acc[r]);
+    for (int r = 0; r < kDecR; ++r) acc[r] = fmaf(w[kOff + r * ORIG + k], t, acc[r]);
   }
   const long long j = j0 + (long long)threadIdx.x * kDecR;
 #pragma unroll
@@ -135,24 +168,30 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
 }
 
 // ---------------------------------------------------------------------------------------------- k_resample
-constexpr int kRI = 4;                 // rows (input strides) per thread item
-constexpr int kRP = 4;                 // consecutive phases per thread item: one 16-byte tap load + kRI sample loads
-                                       // feed kRI * kRP FMAs
-constexpr int kMaxSmemFloats = 16 * 1024;   // staged input segment per CTA (64 KB)
+constexpr int kRI = 8;                 // rows (input strides) per thread item
+constexpr int kRP = 4;                 // consecutive phases per thread item
+constexpr int kMaxSmemFloats = 24 * 1024;   // staged rows per CTA (96 KB)
 
-// One CTA = `rows` input strides of one clip = rows * new_f outputs.  The input segment
-// x[row0 * orig - width, (row0 + rows - 1) * orig + kw - width) is staged in shared memory (zeros outside the clip);
-// a thread item is (row slot g, phase quad q) and owns rows g, g + ng, g + 2 ng, g + 3 ng (interleaved, so that lanes
-// that differ in g are `orig` floats apart in shared memory) x phases 4 q .. 4 q + 3:
-//   acc[r][c] += xs[row_r * orig + k] * tapsT[k][4 q + c]      over the kw taps;
-// tapsT is phase-minor with the phase count padded to a multiple of 4 (zero taps), so lanes read it coalesced.
+// The polyphase FIR as a tiled [strides x taps] x [taps x phases] product on the FMA pipe.  One CTA = `rows` input
+// strides of one clip x a block of up to 32 phase quads (blockIdx.z), so that the taps a CTA streams (kw x 4 nqb)
+// are shared by all its rows -- through L1: the 8 warps differ in row slot and read the same tap lines.
+// Row i of the tile needs the kw samples x[(row0 + i) * orig - width ...]; each row is staged on its own in shared
+// memory (pitch kwp = kw rounded up to 4, zeros outside the clip and in the pad) so that a thread reads 4 consecutive
+// taps' worth of samples with one 16-byte load.  A thread item is (row slot g, phase quad q): rows g, g + ng, ...,
+// g + 7 ng x phases 4 q .. 4 q + 3; per 4 taps it issues 4 16-byte tap loads (tapsT is tap-major, phases padded to a
+// multiple of 4 with zero taps, so the lanes of a warp -- consecutive q -- read it coalesced) and 8 16-byte sample
+// loads (the same address across the lanes that share g: a broadcast) for 128 FMAs.
+// (Tried and dropped, B200 timings for 64 x 10 s at 320->441 / 147->80: register prefetch of the next taps 0.36 /
+//  0.29 ms; 8 x 8 register tile with a 4-stage cp.async tap ring in shared memory 0.44 / 0.40 ms; this form 0.42 /
+//  0.23 ms.)
 template <typename TIn>
 __global__ void __launch_bounds__(kThreads) k_resample(const TIn* __restrict__ x, long long row_stride, int channels,
                                                        const long long* __restrict__ lengths, long long L,
                                                        const float* __restrict__ tapsT, int orig, int new_f, int new_pad,
-                                                       int width, int kw, int rows, float* __restrict__ out,
-                                                       long long out_stride, long long out_cols, int clip) {
-  extern __shared__ float xs[];
+                                                       int width, int kw, int kwp, int rows, int nqb,
+                                                       float* __restrict__ out, long long out_stride,
+                                                       long long out_cols, int clip) {
+  extern __shared__ __align__(16) float xs[];
   const int b = blockIdx.y;
   const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
   const long long olen = (len * new_f + orig - 1) / orig;          // ceil(new * len / orig)
@@ -162,41 +201,53 @@ __global__ void __launch_bounds__(kThreads) k_resample(const TIn* __restrict__ x
   if (j0 >= out_cols) return;
   const long long jend = min(j0 + (long long)rows * new_f, out_cols);
   if (j0 >= olen) {                                                // tile entirely past this clip: zero fill
-    for (long long j = j0 + threadIdx.x; j < jend; j += kThreads) dst[j] = 0.f;
+    if (blockIdx.z == 0)
+      for (long long j = j0 + threadIdx.x; j < jend; j += kThreads) dst[j] = 0.f;
     return;
   }
   const TIn* src = x + (long long)b * row_stride;
-  const long long s0 = row0 * orig - width;
-  const int seg = (rows - 1) * orig + kw;
-  for (int i = threadIdx.x; i < seg; i += kThreads) {
-    const long long s = s0 + i;
-    xs[i] = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = warp; i < rows; i += kThreads / 32) {
+    const long long s0 = (row0 + i) * orig - width;
+    float* xrow = xs + i * kwp;
+    for (int k = lane; k < kwp; k += 32) {
+      const long long s = s0 + k;
+      xrow[k] = (k < kw && s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+    }
   }
   __syncthreads();
   const int ng = rows / kRI;
   const int nq = new_pad / kRP;
-  const int items = ng * nq;
+  const int q0 = blockIdx.z * nqb;                  // this CTA's block of phase quads
+  const int nql = min(nqb, nq - q0);
+  const int items = ng * nql;
+  const int k4n = kwp >> 2;
   for (int it = threadIdx.x; it < items; it += kThreads) {
-    const int g = it / nq, q = it - g * nq;
+    const int g = it / nql, q = q0 + it - g * nql;
     float acc[kRI][kRP];
-    const float* xr[kRI];
 #pragma unroll
-    for (int r = 0; r < kRI; ++r) {
-      xr[r] = xs + (g + r * ng) * orig;
+    for (int r = 0; r < kRI; ++r)
 #pragma unroll
       for (int c = 0; c < kRP; ++c) acc[r][c] = 0.f;
-    }
     const float4* tp = reinterpret_cast<const float4*>(tapsT) + q;
-#pragma unroll 4
-    for (int k = 0; k < kw; ++k) {
-      const float4 t = __ldg(tp + (long long)k * nq);
+    const float4* xp = reinterpret_cast<const float4*>(xs + g * kwp);
+    const int xstep = ng * k4n;                     // float4s between two of this item's rows
+#pragma unroll 1
+    for (int k4 = 0; k4 < k4n; ++k4) {
+      float4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = __ldg(tp + (long long)(4 * k4 + u) * nq);
 #pragma unroll
       for (int r = 0; r < kRI; ++r) {
-        const float v = xr[r][k];
-        acc[r][0] = fmaf(v, t.x, acc[r][0]);
-        acc[r][1] = fmaf(v, t.y, acc[r][1]);
-        acc[r][2] = fmaf(v, t.z, acc[r][2]);
-        acc[r][3] = fmaf(v, t.w, acc[r][3]);
+        const float4 v = xp[r * xstep + k4];
+        const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          acc[r][0] = fmaf(vv[u], t[u].x, acc[r][0]);
+          acc[r][1] = fmaf(vv[u], t[u].y, acc[r][1]);
+          acc[r][2] = fmaf(vv[u], t[u].z, acc[r][2]);
+          acc[r][3] = fmaf(vv[u], t[u].w, acc[r][3]);
+        }
       }
     }
 #pragma unroll
@@ -222,10 +273,12 @@ __global__ void __launch_bounds__(kThreads) k_resample(const TIn* __restrict__ x
 
 struct ttts_resample_plan {
   int orig = 0, new_f = 0, new_pad = 0, width = 0, kw = 0;
+  int kwp = 0;                // kw rounded up to a multiple of 4 (row pitch of the staged tile, rows of d_tapsT)
   int rows = 0;               // k_resample: input strides per CTA (multiple of ingest::kRI)
+  int nqb = 0;                // ... and phase quads per CTA (grid.z = ceil(new_pad / 4 / nqb))
   int decimate = 0;           // k_decimate<orig, kw> applies (new == 1, orig in 2..4, torchaudio's default width)
   int device = 0;
-  float* d_tapsT = nullptr;   // [kw][new_pad], phases zero-padded to a multiple of 4
+  float* d_tapsT = nullptr;   // [kwp][new_pad], taps and phases zero-padded to multiples of 4
   ingest::TapsParam taps1;    // the single phase of a decimator
 };
 
@@ -257,30 +310,27 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   if (orig < 1 || new_f < 1 || width < 1) return fail(TTTS_MEL_EINVAL, "bad resample geometry %d -> %d, width %d", orig, new_f, width);
   const int kw = 2 * width + orig;
   const int new_pad = (new_f + ingest::kRP - 1) / ingest::kRP * ingest::kRP;
-  // rows per CTA (k_resample): the staged segment bounds it; among the candidates take the one whose item count
-  // (rows / 4 x phase quads) wastes the fewest of the 256 threads' slots, preferring >= 4096 outputs per tile
-  const long long max_ng = ((ingest::kMaxSmemFloats - kw) / orig + 1) / ingest::kRI;
-  if (max_ng < 1) return fail(TTTS_MEL_EINVAL, "resample %d -> %d: stride too long for the staged segment", orig, new_f);
+  const int kwp = (kw + 3) / 4 * 4;
+  // CTA tile (k_resample): up to 32 phase quads (one warp's lanes) x as many row slots of 8 rows as fill the 256
+  // threads, bounded by the staged tile (rows x kwp floats)
+  const long long max_ng = ingest::kMaxSmemFloats / kwp / ingest::kRI;
+  if (max_ng < 1) return fail(TTTS_MEL_EINVAL, "resample %d -> %d: filter too long for the staged tile", orig, new_f);
   const int nq = new_pad / ingest::kRP;
-  long long want_ng = (4096 / new_f + ingest::kRI - 1) / ingest::kRI;
-  if (want_ng < 8) want_ng = 8;
-  if (want_ng > max_ng) want_ng = max_ng;
-  long long best_ng = want_ng;
-  double best_eff = 0.0;
-  for (long long ng = want_ng; ng <= max_ng && ng <= want_ng * 2; ++ng) {
-    const long long items = ng * nq, slots = (items + ingest::kThreads - 1) / ingest::kThreads * ingest::kThreads;
-    const double eff = (double)items / (double)slots;
-    if (eff > best_eff + 1e-9) { best_eff = eff; best_ng = ng; }
-  }
+  const int npb = (nq + 31) / 32;
+  const int nqb = (nq + npb - 1) / npb;
+  long long best_ng = ingest::kThreads / nqb;
+  if (best_ng < 1) best_ng = 1;
+  if (best_ng > max_ng) best_ng = max_ng;
   auto* p = new (std::nothrow) ttts_resample_plan();
   if (!p) return fail(TTTS_MEL_ENOMEM, "host allocation failed");
-  p->orig = orig; p->new_f = new_f; p->new_pad = new_pad; p->width = width; p->kw = kw;
+  p->orig = orig; p->new_f = new_f; p->new_pad = new_pad; p->width = width; p->kw = kw; p->kwp = kwp;
   p->rows = (int)(best_ng * ingest::kRI);
+  p->nqb = nqb;
   p->decimate = (new_f == 1 && ((orig == 2 && kw == 28) || (orig == 3 && kw == 41) || (orig == 4 && kw == 54))) ? 1 : 0;
   if (getenv("TTTS_RESAMPLE_GENERIC")) p->decimate = 0;
   memset(&p->taps1, 0, sizeof(p->taps1));
   if (p->decimate) memcpy(p->taps1.t, taps, kw * sizeof(float));
-  std::vector<float> t((size_t)kw * new_pad, 0.f);
+  std::vector<float> t((size_t)kwp * new_pad, 0.f);
   for (int ph = 0; ph < new_f; ++ph)
     for (int k = 0; k < kw; ++k) t[(size_t)k * new_pad + ph] = taps[(size_t)ph * kw + k];
   cudaError_t e = cudaGetDevice(&p->device);
@@ -327,8 +377,12 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     const long long gx = (out_cols + ingest::kDecTile - 1) / ingest::kDecTile;
     if (gx > 0x7FFFFFFFLL) return fail(TTTS_MEL_EINVAL, "clip too long");
     dim3 grid((unsigned)gx, (unsigned)B);
+    // 16-byte (float / stereo int16) or 8-byte (mono int16) staging loads need aligned row starts
+    const int64_t unit = sizeof(TIn) == 4 ? 4 : (channels == 2 ? 8 : 4);
+    const uintptr_t align = sizeof(TIn) == 4 ? 16 : (channels == 2 ? 16 : 8);
+    const int vec = (sizeof(TIn) == 4 || channels <= 2) && row_stride % unit == 0 && (uintptr_t)x % align == 0;
 #define TTTS_DEC(O, K) ingest::k_decimate<O, K, TIn><<<grid, ingest::kThreads, 0, st>>>( \
-        x, row_stride, channels, len, L, p->taps1, p->width, out, out_stride, out_cols, clip)
+        x, row_stride, channels, len, L, p->taps1, out, out_stride, out_cols, clip, vec)
     if (p->orig == 2) TTTS_DEC(2, 28);
     else if (p->orig == 3) TTTS_DEC(3, 41);
     else TTTS_DEC(4, 54);
@@ -337,11 +391,12 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     const long long tile = (long long)p->rows * p->new_f;
     const long long gx = (out_cols + tile - 1) / tile;
     if (gx > 0x7FFFFFFFLL) return fail(TTTS_MEL_EINVAL, "clip too long");
-    const size_t smem = ((size_t)(p->rows - 1) * p->orig + p->kw) * sizeof(float);
-    dim3 grid((unsigned)gx, (unsigned)B);
+    const size_t smem = (size_t)p->rows * p->kwp * sizeof(float);
+    const int nq = p->new_pad / ingest::kRP;
+    dim3 grid((unsigned)gx, (unsigned)B, (unsigned)((nq + p->nqb - 1) / p->nqb));
     ingest::k_resample<TIn><<<grid, ingest::kThreads, smem, st>>>(
-        x, row_stride, channels, len, L, p->d_tapsT, p->orig, p->new_f, p->new_pad, p->width, p->kw, p->rows, out,
-        out_stride, out_cols, clip);
+        x, row_stride, channels, len, L, p->d_tapsT, p->orig, p->new_f, p->new_pad, p->width, p->kw, p->kwp, p->rows,
+        p->nqb, out, out_stride, out_cols, clip);
   }
   CUDA_TRY(cudaGetLastError());
   g_launches = 1;
