@@ -105,3 +105,53 @@ def test_two_rank_allreduce_equals_single_rank():
     assert np.array_equal(ret[0], ret[1])                               # every rank derives identical norms
     assert ret[0][160] == single[160] == sum(orc.frame_count(L) for L in lens)
     assert np.allclose(ret[0], single, rtol=1e-12, atol=0)              # fp64 all-reduce == single-rank result
+
+
+def test_mel_pth_sink_writes_the_reference_format(tmp_path):
+    """mel_extract.py:26-27: torch.save(mel.cpu().detach(), f'{wav_file}.mel.pth') with mel [1, n_mels, T] fp32."""
+    from xtts_b200.sweep import mel_pth_done, mel_pth_sink
+    paths = [str(tmp_path / f"clip{i}.wav") for i in range(4)]
+    mel = torch.arange(2 * 5 * 7, dtype=torch.float32).reshape(2, 5, 7)
+    sink, done = mel_pth_sink(paths), mel_pth_done(paths)
+    assert not any(done(i) for i in range(4))
+    sink([3, 1], mel, torch.tensor([7, 4], dtype=torch.int32))
+    assert [done(i) for i in range(4)] == [False, True, False, True]
+    a, b = torch.load(paths[3] + ".mel.pth"), torch.load(paths[1] + ".mel.pth")
+    assert a.shape == (1, 5, 7) and a.dtype == torch.float32 and torch.equal(a[0], mel[0])
+    assert b.shape == (1, 5, 4) and torch.equal(b[0], mel[1, :, :4])
+    assert a.is_contiguous() and a.untyped_storage().nbytes() == a.numel() * 4     # no padded batch behind the file
+    import os
+    assert not [f for f in os.listdir(tmp_path) if f.endswith(".tmp")]
+
+
+@pytest.mark.gpu
+def test_pcm16_corpus_sweep_matches_clip_by_clip_reference(tmp_path):
+    """WAV files -> pcm16_fetch -> MelSweep -> .mel.pth files, against load_audio + the V2 call per clip."""
+    import numpy as np
+    from oracle import ingest_oracle as ing
+    from oracle import mel_oracle as orc
+    from xtts_b200 import MelSpectrogramFeatures
+    from xtts_b200.sweep import MelSweep, mel_pth_done, mel_pth_sink, pcm16_fetch
+    frames = [30000, 52000, 44100, 61000, 30500, 8000]
+    paths = []
+    for i, f in enumerate(frames):
+        p = str(tmp_path / f"u{i}.wav")
+        ing.write_wav(p, ing.synth_pcm16(f, 1 + i % 2, 900 + i, "uniform"), 44100)
+        paths.append(p)
+    mod = MelSpectrogramFeatures()
+    plan = mod._plan_for(torch.device("cuda:0"))
+    lengths = [ing.out_len(f, 44100, 24000) for f in frames]
+    sweep = MelSweep(plan, lengths, sample_rate=24000, max_clips=4)
+    fetch = pcm16_fetch(lambda i: ing.read_wav(paths[i])[0], 44100, 24000, "cuda:0")
+    acc = sweep.run_stats(fetch, done=mel_pth_done(paths), sink=mel_pth_sink(paths))
+    assert float(acc[-1]) == sum(frame_count(l) for l in lengths)
+    for i, p in enumerate(paths):
+        got = torch.load(p + ".mel.pth")
+        wav = ing.callsite_load_audio(ing.read_wav(p)[0], 44100, 24000)
+        ref = orc.callsite_logmel(wav, orc.V2, None)
+        assert got.shape == ref.shape and got.dtype == torch.float32
+        assert float((got - ref).abs().max()) <= 2e-3     # log of |.| amplifies the 3e-7 resample tolerance near the clamp
+    # resume: everything exists now, nothing is fetched again
+    calls = []
+    sweep.run_stats(lambda idx, m: calls.append(idx), done=mel_pth_done(paths))
+    assert calls == []

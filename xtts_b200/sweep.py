@@ -136,3 +136,54 @@ class MelSweep:
             if sink is not None:
                 sink(idx, mel.transpose(1, 2), n_frames)
         return allreduce_stats(acc)
+
+
+def mel_pth_sink(paths: Sequence[str], suffix: str = ".mel.pth") -> Callable:
+    """``sink`` that writes what ``process_mel`` writes (mel_extract.py:9,26-27): one file ``<wav path>.mel.pth``
+    per clip holding ``torch.save`` of a CPU float32 tensor ``[1, n_mels, T]`` (that clip's frames only).  One
+    device->host copy per batch; the per-file slices are views of it."""
+    import os
+
+    def sink(indices, mel_bct: torch.Tensor, n_frames: torch.Tensor) -> None:
+        host = mel_bct.to("cpu", non_blocking=False)
+        counts = n_frames.to("cpu").tolist()
+        for b, i in enumerate(indices):
+            out = paths[i] + suffix
+            tmp = out + ".tmp"
+            torch.save(host[b:b + 1, :, :counts[b]].contiguous().clone(), tmp)
+            os.replace(tmp, out)         # a killed sweep never leaves a truncated file for the resume rule to skip
+
+    return sink
+
+
+def mel_pth_done(paths: Sequence[str], suffix: str = ".mel.pth") -> Callable[[int], bool]:
+    """The reference's skip-if-exists resume rule (mel_extract.py:10-12)."""
+    import os
+    return lambda i: os.path.exists(paths[i] + suffix)
+
+
+def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, *, kernel_dtype=torch.float32,
+                pinned: bool = True) -> Callable:
+    """``fetch`` for corpora of 16-bit PCM: ``read_pcm(i) -> int16 array [frames, channels]`` (the file decode, host
+    I/O) -> one pinned ``[B, F, C]`` batch -> one H2D copy of int16 -> ``load_audio_pcm16`` (channel 0, sinc
+    resample, clip: utils.py:32-47) on the device.  ``max_len`` is in samples at the TARGET rate (what the buckets
+    are built from); the batch is padded to the longest source clip."""
+    from .ingest import load_audio_pcm16
+
+    def fetch(indices, max_len):
+        import numpy as np
+        clips = [torch.from_numpy(np.array(read_pcm(i), dtype=np.int16, copy=True)) for i in indices]
+        clips = [c[:, None] if c.dim() == 1 else c for c in clips]
+        F = max(int(c.shape[0]) for c in clips)
+        C = int(clips[0].shape[1])
+        host = torch.zeros((len(clips), F, C), dtype=torch.int16, pin_memory=pinned)
+        for b, c in enumerate(clips):
+            if int(c.shape[1]) != C:
+                c = c[:, :1].expand(-1, C)      # only channel 0 is read
+            host[b, :c.shape[0]] = c
+        frames = torch.tensor([int(c.shape[0]) for c in clips], dtype=torch.int64)
+        wav, lens = load_audio_pcm16(host.to(device, non_blocking=True), source_rate, target_rate, frames,
+                                     kernel_dtype=kernel_dtype)
+        return wav, lens
+
+    return fetch
