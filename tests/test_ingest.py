@@ -288,3 +288,42 @@ def test_gpu_c_abi_argument_errors():
     assert lib.ttts_resample_forward(rs._h, x.data_ptr(), 4, None, 1, 8, x.data_ptr(), 8, 0, None) == _cabi.EINVAL
     assert lib.ttts_resample_forward(rs._h, x.data_ptr(), 8, None, 1, 8, x.data_ptr(), 3, 0, None) == _cabi.EINVAL
     assert lib.ttts_resample_out_len(rs._h, 9) == 5
+
+
+@gpu
+@pytest.mark.parametrize("rates", [(44100, 22050), (48000, 16000), (44100, 24000), (16000, 22050), (16000, 24000)])
+def test_gpu_kernels_stay_inside_their_rows(rates):
+    """Guard bands (compute-sanitizer is not available on the pool): every output row sits in a sentinel-filled
+    buffer with an odd pitch; nothing outside [0, out_len) of a row may change, for fp32 and int16 input."""
+    from xtts_b200 import _cabi, Resampler
+    lib = _cabi.lib()
+    o, n = rates
+    rs = Resampler(o, n)
+    B, L, C = 3, 10007, 2
+    Lo = rs.out_len(L)
+    pitch, lead = Lo + 13, 5
+    stream = torch.cuda.current_stream().cuda_stream
+    x = torch.rand((B, L), device="cuda") * 2 - 1
+    pcm = torch.randint(-32768, 32767, (B, L, C), dtype=torch.int16, device="cuda")
+    lens = torch.tensor([L, 1, 5000], dtype=torch.int64, device="cuda")
+    for src in ("f32", "pcm16"):
+        buf = torch.full((B * pitch + lead + 7,), 777.0, device="cuda")
+        out_ptr = buf.data_ptr() + 4 * lead
+        if src == "f32":
+            _cabi.check(lib.ttts_resample_forward(rs._h, x.data_ptr(), L, lens.data_ptr(), B, L, out_ptr, pitch, 0, stream))
+        else:
+            _cabi.check(lib.ttts_resample_pcm16_forward(rs._h, pcm.data_ptr(), L * C, C, lens.data_ptr(), B, L, out_ptr,
+                                                        pitch, 0, stream))
+        torch.cuda.synchronize()
+        body = buf[lead:lead + B * pitch].view(B, pitch)
+        assert bool((buf[:lead] == 777.0).all()) and bool((buf[lead + B * pitch:] == 777.0).all())
+        assert bool((body[:, Lo:] == 777.0).all())
+        assert bool((body[:, :Lo] != 777.0).all())           # every sample of every row was written (zeros past a clip)
+        for b, l in enumerate(lens.cpu().tolist()):
+            assert not body[b, rs.out_len(l):Lo].any()
+    # decode: same idea
+    buf = torch.full((B * (L + 9) + 3,), 777.0, device="cuda")
+    _cabi.check(lib.ttts_pcm16_to_f32(pcm.data_ptr(), L * C, C, lens.data_ptr(), B, L, buf.data_ptr() + 12, L + 9, stream))
+    torch.cuda.synchronize()
+    body = buf[3:].view(B, L + 9)
+    assert bool((buf[:3] == 777.0).all()) and bool((body[:, L:] == 777.0).all()) and bool((body[:, :L] != 777.0).all())
