@@ -369,6 +369,9 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
   if (B <= 0 || L <= 0 || channels <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d L=%lld channels=%d)", B, (long long)L, channels);
   if (B > 65535) return fail(TTTS_MEL_EINVAL, "B %d > 65535: split the batch", B);
   if (row_stride < L * channels) return fail(TTTS_MEL_EINVAL, "row_stride %lld < L %lld x channels %d", (long long)row_stride, (long long)L, channels);
+  int cur_dev = -1;
+  CUDA_TRY(cudaGetDevice(&cur_dev));
+  if (cur_dev != p->device) return fail(TTTS_MEL_EINVAL, "plan lives on device %d, the current device is %d", p->device, cur_dev);
   const long long out_cols = ttts_resample_out_len(p, L);
   if (out_stride < out_cols) return fail(TTTS_MEL_EINVAL, "out_row_stride %lld < %lld output samples", (long long)out_stride, out_cols);
   cudaStream_t st = (cudaStream_t)stream;

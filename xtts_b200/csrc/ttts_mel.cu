@@ -1268,6 +1268,9 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   if (!p || !wav || !out || !ws_ptr) return fail(TTTS_MEL_EINVAL, "null argument");
   if (B <= 0 || Lmax <= 0 || Tmax <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d Lmax=%lld Tmax=%d)", B, (long long)Lmax, Tmax);
   if (row_stride < Lmax) return fail(TTTS_MEL_EINVAL, "row_stride %lld < Lmax %lld", (long long)row_stride, (long long)Lmax);
+  int cur_dev = -1;
+  CUDA_TRY(cudaGetDevice(&cur_dev));
+  if (cur_dev != p->device) return fail(TTTS_MEL_EINVAL, "plan lives on device %d, the current device is %d", p->device, cur_dev);
   if (ttts_mel_frames(p, Lmax) < 0) return TTTS_MEL_EINVAL;
   Workspace w = carve(p, ws_ptr, B, Lmax);
   if (ws_bytes < w.bytes) return fail(TTTS_MEL_ENOMEM, "workspace %zu < %zu bytes", ws_bytes, w.bytes);
