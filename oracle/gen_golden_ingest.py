@@ -40,11 +40,16 @@ CASES = [
 ]
 
 
+PROMPT_LENGTHS = (1000, 50000, 72000, 100000, 480000, 700000)
+PROMPT_SEEDS = 5
+
+
 def main():
     sys.path.insert(0, REF)
     import torchaudio
     torchaudio.load = ing.torchaudio_load_pcm16            # see the module docstring
-    from ttts.utils.utils import load_audio                # the reference
+    from ttts.utils.utils import get_prompt_slice, load_audio    # the reference
+    import random
     torch.set_num_threads(1)
     out = {}
     names = []
@@ -58,6 +63,16 @@ def main():
             out["y_" + name] = y.numpy()
             names.append(name)
             print(f"{name}: {sr} -> {target}, {frames} x {ch} -> {tuple(y.shape)}, max |y| {float(y.abs().max()):.4f}")
+    # get_prompt_slice (utils.py:50-74): (L, is_eval, seed) -> (first sample, length) of the crop of arange(L)
+    crops = []
+    for L in PROMPT_LENGTHS:
+        a = torch.arange(L, dtype=torch.float32)[None]
+        for ev in (0, 1):
+            for seed in range(PROMPT_SEEDS):
+                random.seed(seed)
+                c = get_prompt_slice(a, is_eval=bool(ev))
+                crops.append([L, ev, seed, int(c[0, 0]) if c.shape[1] else 0, int(c.shape[1])])
+    out["prompt_crops"] = np.array(crops, dtype=np.int64)
     dst = os.path.join(ROOT, "tests", "golden", "ingest_load_audio.npz")
     np.savez_compressed(dst, names=np.array(names), cases=np.array([list(map(str, c)) for c in CASES]),
                         torch=torch.__version__, torchaudio=torchaudio.__version__,

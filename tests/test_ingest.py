@@ -99,6 +99,20 @@ def test_host_mirror_argument_errors():
         Resampler(44100, 22050, device="cpu")
 
 
+def test_get_prompt_slice_crops_like_the_reference(gold):
+    import random
+    from xtts_b200.ingest import get_prompt_slice
+    crops = gold["prompt_crops"]
+    assert len(crops) == 60
+    for L, ev, seed, first, length in crops.tolist():
+        random.seed(seed)
+        c = get_prompt_slice(torch.arange(L, dtype=torch.float32)[None], is_eval=bool(ev))
+        assert c.shape == (1, length) and (length == 0 or int(c[0, 0]) == first)
+    a = torch.zeros(2, 100000)
+    assert get_prompt_slice(a, is_eval=True).shape == (2, 100000)           # shorter than the mid length: whole clip
+    assert get_prompt_slice(torch.zeros(1, 700000), is_eval=True).shape == (1, 276000)
+
+
 def test_out_len_is_ceil():
     for o, n in [(44100, 22050), (16000, 22050), (44100, 24000)]:
         for L in (1, 2, 3, 319, 320, 321, 44099, 44100, 44101):

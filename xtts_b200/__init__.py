@@ -5,10 +5,10 @@ Only the hot path: ``TorchMelSpectrogram`` / ``MelSpectrogramFeatures`` / ``dvae
 ``libttts_mel.so`` (``csrc/ttts_mel.cu`` behind the C ABI of ``include/ttts_mel.h``), and the ingestion step in
 front of it (``ingest.py``: int16 PCM -> float32 channel 0 -> sinc resample -> clip, ``include/ttts_ingest.h``).
 """
-from .ingest import Resampler, decode_pcm16, load_audio_pcm16, sinc_resample_taps
+from .ingest import Resampler, decode_pcm16, get_prompt_slice, load_audio_pcm16, sinc_resample_taps
 from .mel import (DEFAULT_MEL_NORM_FILE, MelPlan, MelSpectrogramFeatures, MelSpectrogramFeatures1,
                   TorchMelSpectrogram, dvae_wav_to_mel, make_pad_mask, mel_spectrogram)
 
 __all__ = ["DEFAULT_MEL_NORM_FILE", "MelPlan", "MelSpectrogramFeatures", "MelSpectrogramFeatures1",
            "TorchMelSpectrogram", "dvae_wav_to_mel", "make_pad_mask", "mel_spectrogram",
-           "Resampler", "decode_pcm16", "load_audio_pcm16", "sinc_resample_taps"]
+           "Resampler", "decode_pcm16", "get_prompt_slice", "load_audio_pcm16", "sinc_resample_taps"]

@@ -231,3 +231,21 @@ def load_audio_pcm16(pcm: torch.Tensor, sr: int, sampling_rate: int, frames: Opt
     if frames is not None:
         return wav, out_len
     return wav
+
+
+def get_prompt_slice(audio: torch.Tensor, max_audio_length: float = 20, min_audio_length: float = 3,
+                     sample_rate: int = 24000, is_eval: bool = False) -> torch.Tensor:
+    """Conditioning-prompt crop of ``[C, L]`` audio (utils.py:50-74), a view -- works on device tensors as is.
+
+    Training: a length drawn uniformly from [min, max] seconds (half the clip when the clip is shorter than the
+    draw), at a uniformly drawn start; eval: the mid length (the whole clip when shorter) from sample 0.  Draws
+    come from Python's ``random`` in the reference's order (length, then start), so a seeded run crops identically.
+    """
+    import random
+    longest, shortest = max_audio_length * sample_rate, min_audio_length * sample_rate
+    total = audio.shape[-1]
+    want = int((shortest + longest) / 2) if is_eval else random.randint(shortest, longest)
+    if want > total:
+        want = total if is_eval else total // 2
+    start = 0 if is_eval else random.randint(0, total - want)
+    return audio[:, start:start + want]
