@@ -139,8 +139,9 @@ int32_t ttts_mel_last_launch_count(void);
 int ttts_mel_profile_enable(int32_t max_calls);
 int ttts_mel_profile_collect(float* ms_out, int32_t capacity);
 
-/* Timing experiments for kernel development (RESULTS ARE INVALID while a flag is set): bit 0 removes the
- * converter -> MMA operand handoff, bit 1 the basis loads, bit 2 the epilogue.  0 restores normal operation. */
+/* Timing experiments for kernel development (RESULTS ARE INVALID while a flag is set; tools/gpu_experiments.py):
+ * 1 removes the converter -> MMA operand handoff, 2 the basis loads, 4 the epilogue, 8 the drain arithmetic (the
+ * accumulators are still read), 16 the log pass, 32 the MMAs themselves.  0 restores normal operation. */
 void ttts_mel_set_experiment(int32_t flags);
 
 const char* ttts_mel_last_error(void);
