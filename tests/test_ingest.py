@@ -254,6 +254,26 @@ def test_gpu_decimator_agrees_with_general_kernel(monkeypatch):
 
 
 @gpu
+@pytest.mark.parametrize("rates", [(44100, 24000), (16000, 22050), (24000, 22050), (44100, 16000), (48000, 22050)])
+def test_gpu_tensor_core_resampler_agrees_with_fma_kernel(monkeypatch, rates):
+    """k_resample_tc (tcgen05, 3xTF32) against k_resample (fp32 FMA) on the same plan inputs, ragged."""
+    from xtts_b200 import Resampler
+    o, n = rates
+    x = torch.rand((6, 40013), device="cuda") * 2 - 1
+    lens = torch.tensor([40013, 1, 2, 33333, 4099, 20000])
+    fast = Resampler(o, n)
+    monkeypatch.setenv("TTTS_RESAMPLE_SIMT", "1")
+    slow = Resampler(o, n)
+    monkeypatch.delenv("TTTS_RESAMPLE_SIMT")
+    ya, la = fast(x, lens, clip=True)
+    yb, lb = slow(x, lens, clip=True)
+    assert torch.equal(la, lb)
+    assert float((ya - yb).abs().max()) <= RESAMPLE_TOL
+    for b, l in enumerate(la.cpu().tolist()):
+        assert not ya[b, l:].any()
+
+
+@gpu
 def test_gpu_full_size_linearity_and_dc_gain():
     """BASELINE-sized batch (64 clips x 10 s at 44.1 kHz): size-independent properties -- linearity, and a
     constant stays constant away from the edges (unit DC gain of every phase)."""

@@ -267,6 +267,8 @@ __global__ void __launch_bounds__(kThreads) k_resample(const TIn* __restrict__ x
   }
 }
 
+#include "k_resample_tc.cuh"
+
 }  // namespace ingest
 
 // ------------------------------------------------------------------------------------------------ host / C ABI
@@ -280,6 +282,10 @@ struct ttts_resample_plan {
   int device = 0;
   float* d_tapsT = nullptr;   // [kwp][new_pad], taps and phases zero-padded to multiples of 4
   ingest::TapsParam taps1;    // the single phase of a decimator
+  int tc = 0;                 // k_resample_tc applies (>= 16 phases; TTTS_RESAMPLE_SIMT=1 forces k_resample)
+  int ksteps = 0, npass = 0, nbp = 0, num_sms = 0;
+  float* d_tapsB = nullptr;   // [npass][ksteps][hi | lo][2 k-halves][nbp][4] TF32-exact hi, remainder lo
+  int32_t* d_status = nullptr;
 };
 
 extern "C" int ttts_pcm16_to_f32(const int16_t* pcm, int64_t in_stride, int32_t channels, const int64_t* frames_b,
@@ -334,6 +340,44 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   for (int ph = 0; ph < new_f; ++ph)
     for (int k = 0; k < kw; ++k) t[(size_t)k * new_pad + ph] = taps[(size_t)ph * kw + k];
   cudaError_t e = cudaGetDevice(&p->device);
+  // tensor-core path: phases in blocks of <= 192 (multiples of 16), taps in k-steps of 8, split hi / lo
+  p->tc = (new_f >= 16 && !p->decimate && !getenv("TTTS_RESAMPLE_SIMT")) ? 1 : 0;
+  std::vector<float> tb;
+  if (p->tc) {
+    p->npass = (new_f + ingest::tc::kMaxNb - 1) / ingest::tc::kMaxNb;
+    p->nbp = ((new_f + p->npass - 1) / p->npass + 15) / 16 * 16;
+    p->ksteps = (kw + 7) / 8;
+    const size_t arr = (size_t)2 * p->nbp * 4;
+    tb.assign((size_t)p->npass * p->ksteps * 2 * arr, 0.f);
+    for (int pb = 0; pb < p->npass; ++pb)
+      for (int ks = 0; ks < p->ksteps; ++ks) {
+        float* stage = tb.data() + ((size_t)pb * p->ksteps + ks) * 2 * arr;
+        for (int n = 0; n < p->nbp; ++n)
+          for (int kk = 0; kk < 8; ++kk) {
+            const int ph = pb * p->nbp + n, k = 8 * ks + kk;
+            if (ph >= new_f || k >= kw) continue;
+            const float v = taps[(size_t)ph * kw + k];
+            uint32_t u;
+            memcpy(&u, &v, 4);
+            u &= 0xFFFFE000u;
+            float hi;
+            memcpy(&hi, &u, 4);
+            const size_t at = ((size_t)(kk >> 2) * p->nbp + n) * 4 + (kk & 3);
+            stage[at] = hi;
+            stage[arr + at] = v - hi;
+          }
+      }
+    cudaDeviceProp prop;
+    if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, p->device);
+    if (e == cudaSuccess) p->num_sms = prop.multiProcessorCount;
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_tapsB, tb.size() * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_tapsB, tb.data(), tb.size() * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_status, sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMemset(p->d_status, 0, sizeof(int32_t));
+    const int dyn = (int)ingest::tc::smem_bytes(p->nbp);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::tc::k_resample_tc<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::tc::k_resample_tc<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+  }
   if (e == cudaSuccess) e = cudaMalloc(&p->d_tapsT, t.size() * sizeof(float));
   if (e == cudaSuccess) e = cudaMemcpy(p->d_tapsT, t.data(), t.size() * sizeof(float), cudaMemcpyHostToDevice);
   if (e == cudaSuccess)
@@ -352,6 +396,8 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
 extern "C" void ttts_resample_plan_destroy(ttts_resample_plan* p) {
   if (!p) return;
   cudaFree(p->d_tapsT);
+  cudaFree(p->d_tapsB);
+  cudaFree(p->d_status);
   delete p;
 }
 
@@ -390,6 +436,18 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     else if (p->orig == 3) TTTS_DEC(3, 41);
     else TTTS_DEC(4, 54);
 #undef TTTS_DEC
+  } else if (p->tc) {
+    ingest::tc::Params q;
+    q.x = x; q.row_stride = row_stride; q.channels = channels; q.lengths = len; q.L = L; q.B = B;
+    q.orig = p->orig; q.new_f = p->new_f; q.width = p->width; q.kw = p->kw; q.ksteps = p->ksteps;
+    q.npass = p->npass; q.nbp = p->nbp; q.tapsB = p->d_tapsB; q.out = out; q.out_stride = out_stride;
+    q.out_cols = out_cols;
+    const long long rows_total = (out_cols + p->new_f - 1) / p->new_f;
+    q.tiles_per_clip = (int)((rows_total + ingest::tc::kTileM - 1) / ingest::tc::kTileM);
+    q.units = (long long)B * q.tiles_per_clip * p->npass;
+    q.clip = clip; q.status = p->d_status;
+    const int grid = (int)std::min<long long>(p->num_sms, q.units);
+    ingest::tc::k_resample_tc<TIn><<<grid, ingest::tc::kThreadsTc, ingest::tc::smem_bytes(p->nbp), st>>>(q);
   } else {
     const long long tile = (long long)p->rows * p->new_f;
     const long long gx = (out_cols + tile - 1) / tile;

@@ -169,6 +169,7 @@ def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, 
     resample, clip: utils.py:32-47) on the device.  ``max_len`` is in samples at the TARGET rate (what the buckets
     are built from); the batch is padded to the longest source clip."""
     from .ingest import load_audio_pcm16
+    stage = {"buf": None, "free": None}
 
     def fetch(indices, max_len):
         import numpy as np
@@ -176,14 +177,25 @@ def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, 
         clips = [c[:, None] if c.dim() == 1 else c for c in clips]
         F = max(int(c.shape[0]) for c in clips)
         C = int(clips[0].shape[1])
-        host = torch.zeros((len(clips), F, C), dtype=torch.int16, pin_memory=pinned)
+        need = len(clips) * F * C
+        if stage["buf"] is None or stage["buf"].numel() < need:      # one pinned staging buffer, grown on demand
+            stage["buf"] = torch.empty(max(need, 2 * (stage["buf"].numel() if stage["buf"] is not None else 0)),
+                                       dtype=torch.int16, pin_memory=pinned)
+            stage["free"] = None
+        if stage["free"] is not None:
+            stage["free"].synchronize()                              # the previous batch's H2D copy has left the buffer
+        host = stage["buf"][:need].view(len(clips), F, C)
+        host.zero_()
         for b, c in enumerate(clips):
             if int(c.shape[1]) != C:
                 c = c[:, :1].expand(-1, C)      # only channel 0 is read
             host[b, :c.shape[0]] = c
         frames = torch.tensor([int(c.shape[0]) for c in clips], dtype=torch.int64)
-        wav, lens = load_audio_pcm16(host.to(device, non_blocking=True), source_rate, target_rate, frames,
-                                     kernel_dtype=kernel_dtype)
+        dev_pcm = host.to(device, non_blocking=True)
+        if dev_pcm.is_cuda:
+            stage["free"] = torch.cuda.Event()
+            stage["free"].record(torch.cuda.current_stream(dev_pcm.device))
+        wav, lens = load_audio_pcm16(dev_pcm, source_rate, target_rate, frames, kernel_dtype=kernel_dtype)
         return wav, lens
 
     return fetch
