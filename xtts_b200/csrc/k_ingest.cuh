@@ -346,15 +346,15 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   if (p->tc) {
     p->npass = (new_f + ingest::tc::kMaxNb - 1) / ingest::tc::kMaxNb;
     p->nbp = ((new_f + p->npass - 1) / p->npass + 15) / 16 * 16;
-    p->ksteps = (kw + 7) / 8;
-    const size_t arr = (size_t)2 * p->nbp * 4;
-    tb.assign((size_t)p->npass * p->ksteps * 2 * arr, 0.f);
+    p->ksteps = (kw + 15) / 16;                       // pairs of k-steps
+    const size_t arr = (size_t)2 * p->nbp * 4;        // one operand array: [2 k-halves][nbp][4]
+    tb.assign((size_t)p->npass * p->ksteps * 4 * arr, 0.f);
     for (int pb = 0; pb < p->npass; ++pb)
-      for (int ks = 0; ks < p->ksteps; ++ks) {
-        float* stage = tb.data() + ((size_t)pb * p->ksteps + ks) * 2 * arr;
+      for (int pr = 0; pr < p->ksteps; ++pr) {
+        float* stage = tb.data() + ((size_t)pb * p->ksteps + pr) * 4 * arr;       // [k-step of the pair][hi | lo]
         for (int n = 0; n < p->nbp; ++n)
-          for (int kk = 0; kk < 8; ++kk) {
-            const int ph = pb * p->nbp + n, k = 8 * ks + kk;
+          for (int kk = 0; kk < 16; ++kk) {
+            const int ph = pb * p->nbp + n, k = 16 * pr + kk;
             if (ph >= new_f || k >= kw) continue;
             const float v = taps[(size_t)ph * kw + k];
             uint32_t u;
@@ -362,9 +362,10 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
             u &= 0xFFFFE000u;
             float hi;
             memcpy(&hi, &u, 4);
-            const size_t at = ((size_t)(kk >> 2) * p->nbp + n) * 4 + (kk & 3);
-            stage[at] = hi;
-            stage[arr + at] = v - hi;
+            const int h = kk >> 3, k8 = kk & 7;
+            const size_t at = ((size_t)(k8 >> 2) * p->nbp + n) * 4 + (k8 & 3);
+            stage[(2 * h) * arr + at] = hi;
+            stage[(2 * h + 1) * arr + at] = v - hi;
           }
       }
     cudaDeviceProp prop;
@@ -445,7 +446,8 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     const long long rows_total = (out_cols + p->new_f - 1) / p->new_f;
     q.tiles_per_clip = (int)((rows_total + ingest::tc::kTileM - 1) / ingest::tc::kTileM);
     q.units = (long long)B * q.tiles_per_clip * p->npass;
-    q.clip = clip; q.status = p->d_status;
+    q.clip = clip; q.status = p->d_status; q.b_stages = ingest::tc::b_stages(p->nbp);
+    q.exp = getenv("TTTS_RESAMPLE_EXP") ? atoi(getenv("TTTS_RESAMPLE_EXP")) : 0;
     const int grid = (int)std::min<long long>(p->num_sms, q.units);
     ingest::tc::k_resample_tc<TIn><<<grid, ingest::tc::kThreadsTc, ingest::tc::smem_bytes(p->nbp), st>>>(q);
   } else {

@@ -8,12 +8,15 @@
 // (two buffers: the epilogue of unit u overlaps the MMAs of unit u + 1), and the 3xTF32 split (hi = 13 low mantissa bits
 // cleared, lo = x - hi; products lo*hi, hi*lo, hi*hi) that keeps fp32-grade accuracy.
 //
-//   warp 0      B producer: one bulk copy per k-step (taps hi | lo, [2 k-halves][nbp][4] each, K-major SWIZZLE_NONE)
-//   warp 1      MMA issuer (one elected lane), 3 MMAs per k-step
+//   warp 0      B producer: one bulk copy per pair of k-steps (taps hi | lo, [2 k-halves][nbp][4] each, K-major
+//               SWIZZLE_NONE)
+//   warp 1      MMA issuer (one elected lane), 6 MMAs per pair (a stage = a pair of k-steps: the barrier and commit
+//               traffic of a single k-step costs more than its three short MMAs)
 //   warp 2      TMEM allocator
-//   warps 4-11  converters: warp (set, q) owns rows 32 q .. 32 q + 31 for the k-steps == set (mod 2): 8 samples of its
-//               row straight from the waveform (fp32, or int16 PCM scaled while loading), split, 2 x tcgen05.st.x8
-//   warps 12-15 epilogue: tcgen05.ld 32 columns -> per-warp shared-memory transpose -> one 128-byte row segment per
+//   warps 4-15  converters: warp (set, q) owns rows 32 q .. 32 q + 31 for every third pair of k-steps: samples straight
+//               from the waveform (fp32, or int16 PCM scaled while loading; coalesced, transposed through shared
+//               memory), split, 2 x tcgen05.st.x8 per k-step
+//   warps 16-23 epilogue (two per TMEM lane quarter, alternating 32-column blocks): tcgen05.ld 32 columns -> per-warp shared-memory transpose -> one 128-byte row segment per
 //               store instruction (clip, zeros past the clip's end)
 // Work unit = (clip, 128-stride tile, phase block), dealt round-robin to one persistent CTA per SM.
 #pragma once
@@ -21,12 +24,14 @@
 namespace tc {
 
 constexpr int kTileM = 128;
-constexpr int kThreadsTc = 512;
-constexpr int kBStagesTc = 6;
-constexpr int kAStagesTc = 8;          // x 16 TMEM columns (hi 8 | lo 8)
-constexpr int kMaxNb = 192;            // phases per block; two accumulator buffers = 384 columns
-constexpr int kColATc = 2 * kMaxNb;    // A ring: columns 384..511
-constexpr int kWarpConvTc = 4, kWarpEpiTc = 12;
+constexpr int kThreadsTc = 768;        // 4 misc + 12 converter + 8 epilogue warps
+constexpr int kBStagesMax = 16;        // taps ring: as many stages as fit kBRingBytes (the MMAs of a k-step are short,
+constexpr int kBRingBytes = 160 * 1024;   // so the bulk copies' latency needs many stages in flight)
+constexpr int kAStagesTc = 6;          // x 32 TMEM columns: one pair of k-steps, (hi 8 | lo 8) each
+constexpr int kMaxNb = 160;            // phases per block; two accumulator buffers = 320 columns
+constexpr int kColATc = 2 * kMaxNb;    // A ring: columns 320..511
+constexpr int kWarpConvTc = 4, kWarpEpiTc = 16;
+constexpr int kConvSets = 3, kEpiSets = 2;
 constexpr int kTPitch = 33;            // epilogue transpose buffer pitch (floats)
 
 struct Params {
@@ -37,19 +42,21 @@ struct Params {
   long long L;
   int B;
   int orig, new_f, width, kw;
-  int ksteps;                 // ceil(kw / 8)
+  int ksteps;                 // pairs of k-steps (16 taps each): ceil(kw / 16)
   int npass, nbp;             // phase blocks, phases per block (multiple of 16)
-  const float* tapsB;         // [npass][ksteps][hi | lo][2 k-halves][nbp][4]
+  const float* tapsB;         // [npass][pairs][2 k-steps][hi | lo][2 k-halves][nbp][4]
   float* out;
   long long out_stride, out_cols;
   int tiles_per_clip;
   long long units;            // B * tiles_per_clip * npass
   int clip;
+  int b_stages;               // taps ring depth
+  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no taps loads, 4 no epilogue, 32 no MMAs
   int32_t* status;
 };
 
 struct __align__(8) Barriers {
-  uint64_t b_full[kBStagesTc], b_empty[kBStagesTc];
+  uint64_t b_full[kBStagesMax], b_empty[kBStagesMax];
   uint64_t a_full[kAStagesTc], a_empty[kAStagesTc];
   uint64_t acc_full[2], acc_empty[2];
 };
@@ -76,17 +83,19 @@ __device__ __forceinline__ Unit locate(const Params& P, long long u) {
 template <typename TIn>
 __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
   extern __shared__ __align__(1024) uint8_t smem_tc[];
-  const uint32_t b_stage_bytes = (uint32_t)P.nbp * 64u;      // 2 arrays x 2 k-halves x nbp rows x 16 B
+  const uint32_t b_stage_bytes = (uint32_t)P.nbp * 128u;     // 2 k-steps x 2 arrays x 2 k-halves x nbp rows x 16 B
   uint8_t* s_b = smem_tc;
-  float* s_t = reinterpret_cast<float*>(s_b + (size_t)kBStagesTc * b_stage_bytes);     // [4 warps][32][kTPitch]
-  Barriers* bars = reinterpret_cast<Barriers*>(s_t + 4 * 32 * kTPitch);
+  const uint32_t nbs = (uint32_t)P.b_stages;
+  float* s_t = reinterpret_cast<float*>(s_b + (size_t)nbs * b_stage_bytes);     // [8 epilogue warps][32][kTPitch]
+  float* s_c = s_t + 4 * kEpiSets * 32 * kTPitch;                                // [12 converter warps][32][20]
+  Barriers* bars = reinterpret_cast<Barriers*>(s_c + 4 * kConvSets * 32 * 20);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kBStagesTc; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
+    for (int i = 0; i < kBStagesMax; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
     for (int i = 0; i < kAStagesTc; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->acc_full[i]), 1); mbar_init(smem_u32(&bars->acc_empty[i]), 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->acc_full[i]), 1); mbar_init(smem_u32(&bars->acc_empty[i]), 4 * kEpiSets); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -100,13 +109,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
 
   if (warp == 0) {
     // ===== taps producer =====
-    if (lane == 0) {
+    if (lane == 0 && !(P.exp & 2)) {
       uint32_t seq = 0;
       for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
         const Unit un = locate(P, u);
         if (!un.live) continue;
         for (int ks = 0; ks < P.ksteps; ++ks, ++seq) {
-          const uint32_t st = seq % kBStagesTc, use = seq / kBStagesTc;
+          const uint32_t st = seq % nbs, use = seq / nbs;
           mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
           const uint32_t full = smem_u32(&bars->b_full[st]);
           mbar_expect_tx(full, b_stage_bytes);
@@ -129,21 +138,27 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
       if (!un.live) continue;
       const uint32_t abuf = useq & 1, ause_acc = useq >> 1;
       const uint32_t d = tmem + abuf * kMaxNb;
-      mbar_wait(smem_u32(&bars->acc_empty[abuf]), (ause_acc & 1) ^ 1, P.status, 201);
+      if (!(P.exp & 4)) mbar_wait(smem_u32(&bars->acc_empty[abuf]), (ause_acc & 1) ^ 1, P.status, 201);
       for (int ks = 0; ks < P.ksteps; ++ks, ++kseq) {
         const uint32_t as = kseq % kAStagesTc, ause = kseq / kAStagesTc;
-        const uint32_t st = kseq % kBStagesTc, use = kseq / kBStagesTc;
-        mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
-        mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
+        const uint32_t st = kseq % nbs, use = kseq / nbs;
+        if (!(P.exp & 1)) mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
+        if (!(P.exp & 2)) mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
         tc_fence_after();
         if (elect_one_sync()) {
-          const uint32_t a_hi = tmem + kColATc + as * 16, a_lo = a_hi + 8;
+          const uint32_t a0 = tmem + kColATc + as * 32;
           const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
-          const uint64_t b_hi = ((uint64_t)desc_hi << 32) | lo;
-          const uint64_t b_lo = ((uint64_t)desc_hi << 32) | (lo + arr16);
-          mma_tf32_ts(d, a_lo, b_hi, idesc, ks == 0 ? 0u : 1u);     // small terms first
-          mma_tf32_ts(d, a_hi, b_lo, idesc, 1u);
-          mma_tf32_ts(d, a_hi, b_hi, idesc, 1u);
+          if (!(P.exp & 32)) {
+#pragma unroll
+            for (uint32_t h = 0; h < 2; ++h) {               // the two k-steps of the pair; small terms first
+              const uint32_t a_hi = a0 + 16 * h, a_lo = a_hi + 8;
+              const uint64_t b_hi = ((uint64_t)desc_hi << 32) | (lo + 2 * h * arr16);
+              const uint64_t b_lo = ((uint64_t)desc_hi << 32) | (lo + (2 * h + 1) * arr16);
+              mma_tf32_ts(d, a_lo, b_hi, idesc, (ks == 0 && h == 0) ? 0u : 1u);
+              mma_tf32_ts(d, a_hi, b_lo, idesc, 1u);
+              mma_tf32_ts(d, a_hi, b_hi, idesc, 1u);
+            }
+          }
           tc_commit(smem_u32(&bars->b_empty[st]));
           tc_commit(smem_u32(&bars->a_empty[as]));
           if (ks == P.ksteps - 1) tc_commit(smem_u32(&bars->acc_full[abuf]));
@@ -152,82 +167,119 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
       }
       ++useq;
     }
-  } else if (warp >= kWarpConvTc && warp < kWarpEpiTc) {
+  } else if (warp >= kWarpConvTc && warp < kWarpEpiTc && !(P.exp & 1)) {
     // ===== converters =====
-    const int set = (warp - kWarpConvTc) >> 2, q = warp & 3;
+    // Iteration `it` of set `set` (of 3) covers the pair of k-steps (16 taps) 3 it + set.  The 32 rows x
+    // 16 samples a warp needs per iteration are 32 segments of 64 bytes, `orig` samples apart: they are loaded
+    // coalesced (a lane takes sample lane & 15 of rows 2 i + (lane >> 4): two segments per load instruction instead of
+    // 32), one iteration ahead, transposed through a per-warp shared-memory tile, and each lane then reads its own
+    // row back, splits it and stores it to TMEM.  Tiles whose whole sample range lies inside the clip (all but the
+    // first and last of a clip) load unmasked.
+    constexpr int kPer = 2, kS = 8 * kPer, kCP = 20;               // kCP: tile pitch (floats), conflict-free 16 B reads
+    const int cw = warp - kWarpConvTc, set = cw >> 2, q = warp & 3;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    float* ct = s_c + cw * 32 * kCP;
     const TIn* xin = reinterpret_cast<const TIn*>(P.x);
+    const int iters = (P.ksteps + kConvSets - 1) / kConvSets;      // pairs per set, rounded up
+    const int lj = lane & 15, lr = lane >> 4;
+    const long long rstep = 2LL * P.orig * P.channels;             // elements between the rows of consecutive loads
     uint32_t kseq = 0;
     for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
       const Unit un = locate(P, u);
       if (!un.live) continue;
-      const TIn* src = xin + (long long)un.b * P.row_stride;
-      const long long s0 = (un.row0 + q * 32 + lane) * P.orig - P.width;
-      auto fetch = [&](int ks, float (&v)[8]) {
+      const long long sl = (un.row0 + q * 32 + lr) * P.orig - P.width + lj;    // my sample of row lr at tap 0
+      const TIn* lp = xin + (long long)un.b * P.row_stride + sl * P.channels;
+      const bool interior = un.row0 * P.orig - P.width >= 0 &&
+                            (un.row0 + kTileM - 1) * P.orig - P.width + (long long)iters * kConvSets * kS <= un.len;
+      auto fetch = [&](int it, float (&v)[kS]) {
+        const int k0 = kS * (kConvSets * it + set);
+        const TIn* pk = lp + (long long)k0 * P.channels;
+        if (interior) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const long long s = s0 + 8 * ks + j;
-          v[j] = (ks < P.ksteps && s >= 0 && s < un.len) ? load_sample(src, s, P.channels) : 0.f;
+          for (int i = 0; i < kS; ++i) v[i] = load_sample(pk + i * rstep, 0, 1);
+        } else {
+#pragma unroll
+          for (int i = 0; i < kS; ++i) {
+            const long long sj = sl + k0 + 2LL * i * P.orig;
+            v[i] = (it < iters && sj >= 0 && sj < un.len) ? load_sample(pk + i * rstep, 0, 1) : 0.f;
+          }
         }
       };
-      float cur[8], nxt[8];
-      fetch(set, cur);
-      for (int ks = set; ks < P.ksteps; ks += 2) {
-        fetch(ks + 2, nxt);                                 // in flight while this k-step is split and stored
-        uint32_t hi[8], lo[8];
+      float cur[kS], nxt[kS];
+      fetch(0, cur);
+      for (int it = 0; it < iters; ++it) {
+        if (it + 1 < iters || !interior) fetch(it + 1, nxt);
+        __syncwarp();                                        // the previous iteration's reads of the tile are done
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t h = __float_as_uint(cur[j]) & 0xFFFFE000u;
-          hi[j] = h;
-          lo[j] = __float_as_uint(cur[j] - __uint_as_float(h));
-        }
-        const uint32_t ksq = kseq + ks;
-        const uint32_t as = ksq % kAStagesTc, ause = ksq / kAStagesTc;
-        const uint32_t a_base = tmem + lane_addr + kColATc + as * 16;
-        mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
-        tc_fence_after();
-        tmem_st8(a_base, hi);
-        tmem_st8(a_base + 8, lo);
-        tmem_wait_st();
-        tc_fence_before();
+        for (int i = 0; i < kS; ++i) ct[(2 * i + lr) * kCP + lj] = cur[i];
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
+        float row[kS];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
+        for (int c = 0; c < kS / 4; ++c) {
+          const float4 v4 = *reinterpret_cast<const float4*>(ct + lane * kCP + 4 * c);
+          row[4 * c] = v4.x; row[4 * c + 1] = v4.y; row[4 * c + 2] = v4.z; row[4 * c + 3] = v4.w;
+        }
+        const int pr = kConvSets * it + set;                  // my pair of k-steps
+        if (pr < P.ksteps) {
+          const uint32_t psq = kseq + pr;
+          const uint32_t as = psq % kAStagesTc, ause = psq / kAStagesTc;
+          const uint32_t a_base = tmem + lane_addr + kColATc + as * 32;
+          uint32_t hi[kS], lo[kS];
+#pragma unroll
+          for (int j = 0; j < kS; ++j) {
+            const uint32_t hb = __float_as_uint(row[j]) & 0xFFFFE000u;
+            hi[j] = hb;
+            lo[j] = __float_as_uint(row[j] - __uint_as_float(hb));
+          }
+          mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
+          tc_fence_after();
+          tmem_st8(a_base, hi);
+          tmem_st8(a_base + 8, lo);
+          tmem_st8(a_base + 16, hi + 8);
+          tmem_st8(a_base + 24, lo + 8);
+          tmem_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
+        }
+#pragma unroll
+        for (int j = 0; j < kS; ++j) cur[j] = nxt[j];
       }
       kseq += P.ksteps;
     }
-  } else if (warp >= kWarpEpiTc) {
+  } else if (warp >= kWarpEpiTc && !(P.exp & 4)) {
     // ===== epilogue =====
-    const int q = warp & 3;
+    const int q = warp & 3, es = (warp - kWarpEpiTc) >> 2;       // TMEM lane quarter, column-block parity
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    float* tb = s_t + q * 32 * kTPitch;
+    float* tb = s_t + (warp - kWarpEpiTc) * 32 * kTPitch;
     uint32_t useq = 0;
     for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
       const Unit un = locate(P, u);
-      float* dst = P.out + (long long)un.b * P.out_stride;
       const int p0 = un.pass * P.nbp;
       const int pn = min(P.nbp, P.new_f - p0);               // valid phases of this block
-      const long long rbase = un.row0 + q * 32;               // first stride of my 32 rows
+      // my 32 rows start at output sample j0 of the clip; everything below is relative to it (32-bit)
+      const long long j0 = (un.row0 + q * 32) * P.new_f + p0;
+      float* dst = P.out + (long long)un.b * P.out_stride + j0;
+      const long long room = P.out_cols - j0, keep = un.olen - j0;     // samples that exist / that are not zero
       if (!un.live) {
         // tile past the clip's end: zeros, row segments of this phase block
-        for (int rr = 0; rr < 32; ++rr) {
-          const long long j0 = (rbase + rr) * P.new_f + p0;
+        for (int rr = es; rr < 32; rr += kEpiSets)
           for (int c = lane; c < pn; c += 32)
-            if (j0 + c < P.out_cols) dst[j0 + c] = 0.f;
-        }
+            if ((long long)rr * P.new_f + c < room) dst[rr * P.new_f + c] = 0.f;
         continue;
       }
       const uint32_t abuf = useq & 1;
       mbar_wait(smem_u32(&bars->acc_full[abuf]), (useq >> 1) & 1, P.status, 501);
       tc_fence_after();
       const uint32_t t_acc = tmem + lane_addr + abuf * kMaxNb;
-      for (int c0 = 0; c0 < P.nbp; c0 += 32) {
+      const int nblk = (P.nbp + 31) >> 5;
+      for (int blk = es; blk < nblk; blk += kEpiSets) {
+        const int c0 = blk * 32;
         uint32_t va[16], vb[16];
         tmem_ld16(t_acc + c0, va);
         if (c0 + 16 < P.nbp) tmem_ld16(t_acc + c0 + 16, vb);
         tmem_wait_ld();
-        if (c0 + 32 >= P.nbp) {                              // my accumulator columns are in registers
+        if (blk + kEpiSets >= nblk) {                        // my last accumulator columns are in registers
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty[abuf]));
@@ -241,16 +293,21 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
         __syncwarp();
         const int c = c0 + lane;
         if (c < pn) {
+#pragma unroll 8
           for (int rr = 0; rr < 32; ++rr) {
-            const long long j = (rbase + rr) * P.new_f + p0 + c;
-            if (j < P.out_cols) {
-              float v = j < un.olen ? tb[rr * kTPitch + lane] : 0.f;
-              if (P.clip) v = fminf(fmaxf(v, -1.f), 1.f);
-              dst[j] = v;
-            }
+            const long long jr = (long long)rr * P.new_f + c;
+            float v = tb[rr * kTPitch + lane];
+            if (jr >= keep) v = 0.f;
+            if (P.clip) v = fminf(fmaxf(v, -1.f), 1.f);
+            if (jr < room) dst[jr] = v;
           }
         }
         __syncwarp();
+      }
+      if (es >= nblk) {                                      // fewer column blocks than epilogue sets: nothing to read
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->acc_empty[abuf]));
       }
       ++useq;
     }
@@ -264,8 +321,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
   }
 }
 
+inline int b_stages(int nbp) {
+  const int n = kBRingBytes / (nbp * 128);
+  return n > kBStagesMax ? kBStagesMax : n;
+}
 inline size_t smem_bytes(int nbp) {
-  return (size_t)kBStagesTc * nbp * 64 + 4 * 32 * kTPitch * sizeof(float) + sizeof(Barriers) + 16;
+  return (size_t)b_stages(nbp) * nbp * 128 + (4 * kEpiSets * 32 * kTPitch + 4 * kConvSets * 32 * 20) * sizeof(float) +
+         sizeof(Barriers) + 16;
 }
 
 }  // namespace tc
