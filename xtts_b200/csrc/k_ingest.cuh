@@ -1,7 +1,8 @@
 // k_ingest.cuh -- ingestion in front of the log-mel path (C ABI in include/ttts_ingest.h):
 //   k_pcm16      interleaved int16 PCM -> float32 channel 0 (x / 32768)        HBM-bound: 2 C + 4 bytes per frame
 //   k_decimate   integer-ratio (2:1, 3:1, 4:1) windowed-sinc FIR, one phase     HBM-bound: 4 (or 2 C) ORIG + 4 bytes per output
-//   k_resample   general polyphase windowed-sinc FIR (orig -> new)              FMA-bound: 2 (2 width + orig) flop per output
+//   k_resample_tc general polyphase windowed-sinc FIR (orig -> new, >= 16 phases) on tcgen05 (k_resample_tc.cuh)
+//   k_resample   the same on the FMA pipe (few phases)                          FMA-bound: 2 (2 width + orig) flop per output
 // The two FIR kernels read float32 or (fused decode) interleaved int16 PCM.
 // Reference: load_audio (ttts/utils/utils.py:32-47), mel_extract.py:15-21.  Included at the end of ttts_mel.cu
 // (one shared library); uses its fail() / CUDA_TRY / g_launches.
@@ -346,7 +347,7 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   if (p->tc) {
     p->npass = (new_f + ingest::tc::kMaxNb - 1) / ingest::tc::kMaxNb;
     p->nbp = ((new_f + p->npass - 1) / p->npass + 15) / 16 * 16;
-    p->ksteps = (kw + 15) / 16;                       // pairs of k-steps
+    p->ksteps = (kw + 31) / 32 * 2;                   // pairs of k-steps, rounded up to whole quads
     const size_t arr = (size_t)2 * p->nbp * 4;        // one operand array: [2 k-halves][nbp][4]
     tb.assign((size_t)p->npass * p->ksteps * 4 * arr, 0.f);
     for (int pb = 0; pb < p->npass; ++pb)

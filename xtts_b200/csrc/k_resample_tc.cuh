@@ -8,9 +8,9 @@
 // (two buffers: the epilogue of unit u overlaps the MMAs of unit u + 1), and the 3xTF32 split (hi = 13 low mantissa bits
 // cleared, lo = x - hi; products lo*hi, hi*lo, hi*hi) that keeps fp32-grade accuracy.
 //
-//   warp 0      B producer: one bulk copy per pair of k-steps (taps hi | lo, [2 k-halves][nbp][4] each, K-major
+//   warp 0      B producer: one bulk copy per quad of k-steps (taps hi | lo, [2 k-halves][nbp][4] each, K-major
 //               SWIZZLE_NONE)
-//   warp 1      MMA issuer (one elected lane), 6 MMAs per pair (a stage = a pair of k-steps: the barrier and commit
+//   warp 1      MMA issuer (one elected lane), 12 MMAs per quad (a stage = four k-steps: the barrier and commit
 //               traffic of a single k-step costs more than its three short MMAs)
 //   warp 2      TMEM allocator
 //   warps 4-15  converters: warp (set, q) owns rows 32 q .. 32 q + 31 for every third pair of k-steps: samples straight
@@ -27,7 +27,7 @@ constexpr int kTileM = 128;
 constexpr int kThreadsTc = 768;        // 4 misc + 12 converter + 8 epilogue warps
 constexpr int kBStagesMax = 16;        // taps ring: as many stages as fit kBRingBytes (the MMAs of a k-step are short,
 constexpr int kBRingBytes = 160 * 1024;   // so the bulk copies' latency needs many stages in flight)
-constexpr int kAStagesTc = 6;          // x 32 TMEM columns: one pair of k-steps, (hi 8 | lo 8) each
+constexpr int kAStagesTc = 3;          // x 64 TMEM columns: one quad of k-steps, (hi 8 | lo 8) each
 constexpr int kMaxNb = 160;            // phases per block; two accumulator buffers = 320 columns
 constexpr int kColATc = 2 * kMaxNb;    // A ring: columns 320..511
 constexpr int kWarpConvTc = 4, kWarpEpiTc = 16;
@@ -42,16 +42,16 @@ struct Params {
   long long L;
   int B;
   int orig, new_f, width, kw;
-  int ksteps;                 // pairs of k-steps (16 taps each): ceil(kw / 16)
+  int ksteps;                 // pairs of k-steps (16 taps each), rounded up to even: a stage is a quad (32 taps)
   int npass, nbp;             // phase blocks, phases per block (multiple of 16)
-  const float* tapsB;         // [npass][pairs][2 k-steps][hi | lo][2 k-halves][nbp][4]
+  const float* tapsB;         // [npass][quads][4 k-steps][hi | lo][2 k-halves][nbp][4]
   float* out;
   long long out_stride, out_cols;
   int tiles_per_clip;
   long long units;            // B * tiles_per_clip * npass
   int clip;
   int b_stages;               // taps ring depth
-  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no taps loads, 4 no epilogue, 32 no MMAs
+  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no taps loads, 4 no epilogue, 32 no MMAs, 64 no L2 prefetch
   int32_t* status;
 };
 
@@ -83,7 +83,8 @@ __device__ __forceinline__ Unit locate(const Params& P, long long u) {
 template <typename TIn>
 __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
   extern __shared__ __align__(1024) uint8_t smem_tc[];
-  const uint32_t b_stage_bytes = (uint32_t)P.nbp * 128u;     // 2 k-steps x 2 arrays x 2 k-halves x nbp rows x 16 B
+  const uint32_t b_stage_bytes = (uint32_t)P.nbp * 256u;     // 4 k-steps x 2 arrays x 2 k-halves x nbp rows x 16 B
+  const int nquads = P.ksteps >> 1;
   uint8_t* s_b = smem_tc;
   const uint32_t nbs = (uint32_t)P.b_stages;
   float* s_t = reinterpret_cast<float*>(s_b + (size_t)nbs * b_stage_bytes);     // [8 epilogue warps][32][kTPitch]
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBStagesMax; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
-    for (int i = 0; i < kAStagesTc; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 4); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
+    for (int i = 0; i < kAStagesTc; ++i) { mbar_init(smem_u32(&bars->a_full[i]), 8); mbar_init(smem_u32(&bars->a_empty[i]), 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bars->acc_full[i]), 1); mbar_init(smem_u32(&bars->acc_empty[i]), 4 * kEpiSets); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -110,17 +111,38 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
   if (warp == 0) {
     // ===== taps producer =====
     if (lane == 0 && !(P.exp & 2)) {
+      // The converters read every input sample about once, straight from DRAM: what they can keep in flight (one
+      // iteration of register prefetch per warp) does not cover that latency.  The samples of the unit two rounds
+      // ahead are therefore pulled into L2 here with bulk prefetches (no registers, no shared memory).
+      auto prefetch_unit = [&](long long u) {
+        if (u >= P.units || (P.exp & 64)) return;
+        const Unit un = locate(P, u);
+        if (!un.live) return;
+        const long long esz = (long long)sizeof(TIn) * P.channels;
+        long long sa = un.row0 * P.orig - P.width, sb = (un.row0 + kTileM) * P.orig - P.width + 16LL * P.ksteps;
+        if (sa < 0) sa = 0;
+        if (sb > un.len) sb = un.len;
+        const char* base = reinterpret_cast<const char*>(P.x) + (long long)un.b * P.row_stride * (long long)sizeof(TIn);
+        uintptr_t a0 = ((uintptr_t)(base + sa * esz) + 15) & ~(uintptr_t)15;
+        const uintptr_t a1 = (uintptr_t)(base + sb * esz) & ~(uintptr_t)15;
+        for (; a0 < a1; a0 += 32768) {
+          const uint32_t n = (uint32_t)((a1 - a0) < 32768 ? (a1 - a0) : 32768);
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(n) : "memory");
+        }
+      };
+      prefetch_unit((long long)blockIdx.x + gridDim.x);
       uint32_t seq = 0;
       for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
+        prefetch_unit(u + 2LL * gridDim.x);
         const Unit un = locate(P, u);
         if (!un.live) continue;
-        for (int ks = 0; ks < P.ksteps; ++ks, ++seq) {
+        for (int ks = 0; ks < nquads; ++ks, ++seq) {
           const uint32_t st = seq % nbs, use = seq / nbs;
           mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
           const uint32_t full = smem_u32(&bars->b_full[st]);
           mbar_expect_tx(full, b_stage_bytes);
           bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
-                   P.tapsB + ((size_t)un.pass * P.ksteps + ks) * (b_stage_bytes / 4), b_stage_bytes, full);
+                   P.tapsB + ((size_t)un.pass * nquads + ks) * (b_stage_bytes / 4), b_stage_bytes, full);
         }
       }
     }
@@ -139,18 +161,18 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
       const uint32_t abuf = useq & 1, ause_acc = useq >> 1;
       const uint32_t d = tmem + abuf * kMaxNb;
       if (!(P.exp & 4)) mbar_wait(smem_u32(&bars->acc_empty[abuf]), (ause_acc & 1) ^ 1, P.status, 201);
-      for (int ks = 0; ks < P.ksteps; ++ks, ++kseq) {
+      for (int ks = 0; ks < nquads; ++ks, ++kseq) {
         const uint32_t as = kseq % kAStagesTc, ause = kseq / kAStagesTc;
         const uint32_t st = kseq % nbs, use = kseq / nbs;
         if (!(P.exp & 1)) mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 202);
         if (!(P.exp & 2)) mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 203);
         tc_fence_after();
         if (elect_one_sync()) {
-          const uint32_t a0 = tmem + kColATc + as * 32;
+          const uint32_t a0 = tmem + kColATc + as * 64;
           const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
           if (!(P.exp & 32)) {
 #pragma unroll
-            for (uint32_t h = 0; h < 2; ++h) {               // the two k-steps of the pair; small terms first
+            for (uint32_t h = 0; h < 4; ++h) {               // the four k-steps of the quad; small terms first
               const uint32_t a_hi = a0 + 16 * h, a_lo = a_hi + 8;
               const uint64_t b_hi = ((uint64_t)desc_hi << 32) | (lo + 2 * h * arr16);
               const uint64_t b_lo = ((uint64_t)desc_hi << 32) | (lo + (2 * h + 1) * arr16);
@@ -161,7 +183,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
           }
           tc_commit(smem_u32(&bars->b_empty[st]));
           tc_commit(smem_u32(&bars->a_empty[as]));
-          if (ks == P.ksteps - 1) tc_commit(smem_u32(&bars->acc_full[abuf]));
+          if (ks == nquads - 1) tc_commit(smem_u32(&bars->acc_full[abuf]));
         }
         __syncwarp();
       }
@@ -183,69 +205,95 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
     const int iters = (P.ksteps + kConvSets - 1) / kConvSets;      // pairs per set, rounded up
     const int lj = lane & 15, lr = lane >> 4;
     const long long rstep = 2LL * P.orig * P.channels;             // elements between the rows of consecutive loads
-    uint32_t kseq = 0;
-    for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
-      const Unit un = locate(P, u);
-      if (!un.live) continue;
-      const long long sl = (un.row0 + q * 32 + lr) * P.orig - P.width + lj;    // my sample of row lr at tap 0
-      const TIn* lp = xin + (long long)un.b * P.row_stride + sl * P.channels;
-      const bool interior = un.row0 * P.orig - P.width >= 0 &&
-                            (un.row0 + kTileM - 1) * P.orig - P.width + (long long)iters * kConvSets * kS <= un.len;
-      auto fetch = [&](int it, float (&v)[kS]) {
-        const int k0 = kS * (kConvSets * it + set);
-        const TIn* pk = lp + (long long)k0 * P.channels;
-        if (interior) {
+    // fetch cursor: the (unit, iteration) whose samples are loaded next; it runs one iteration ahead of the consume
+    // cursor and crosses unit boundaries, so the load pipeline never drains between units
+    long long f_u = blockIdx.x, f_sl = 0, f_len = 0;
+    const TIn* f_lp = xin;
+    int f_it = 0;
+    bool f_valid = false, f_interior = false;
+    auto enter = [&](long long u) {                          // first live unit at or after u
+      f_valid = false;
+      for (; u < P.units; u += gridDim.x) {
+        const Unit un = locate(P, u);
+        if (!un.live) continue;
+        f_u = u; f_it = 0; f_valid = true; f_len = un.len;
+        f_sl = (un.row0 + q * 32 + lr) * P.orig - P.width + lj;          // my sample of row lr at tap 0
+        f_lp = xin + (long long)un.b * P.row_stride + f_sl * P.channels;
+        f_interior = un.row0 * P.orig - P.width >= 0 &&
+                     (un.row0 + kTileM - 1) * P.orig - P.width + (long long)iters * kConvSets * kS <= un.len;
+        return;
+      }
+    };
+    auto advance = [&]() { if (++f_it >= iters) enter(f_u + gridDim.x); };
+    auto fetch = [&](float (&v)[kS]) {
+      const int k0 = kS * (kConvSets * f_it + set);
+      const TIn* pk = f_lp + (long long)k0 * P.channels;
+      if (P.exp & 128) {
 #pragma unroll
-          for (int i = 0; i < kS; ++i) v[i] = load_sample(pk + i * rstep, 0, 1);
-        } else {
+        for (int i = 0; i < kS; ++i) v[i] = 0.25f * i;
+      } else if (f_interior) {
 #pragma unroll
-          for (int i = 0; i < kS; ++i) {
-            const long long sj = sl + k0 + 2LL * i * P.orig;
-            v[i] = (it < iters && sj >= 0 && sj < un.len) ? load_sample(pk + i * rstep, 0, 1) : 0.f;
-          }
+        for (int i = 0; i < kS; ++i) v[i] = load_sample(pk + i * rstep, 0, 1);
+      } else {
+#pragma unroll
+        for (int i = 0; i < kS; ++i) {
+          const long long sj = f_sl + k0 + 2LL * i * P.orig;
+          v[i] = (sj >= 0 && sj < f_len) ? load_sample(pk + i * rstep, 0, 1) : 0.f;
         }
-      };
+      }
+    };
+    enter(blockIdx.x);
+    if (f_valid) {
       float cur[kS], nxt[kS];
-      fetch(0, cur);
-      for (int it = 0; it < iters; ++it) {
-        if (it + 1 < iters || !interior) fetch(it + 1, nxt);
+      fetch(cur);
+      long long c_u = f_u;
+      int c_it = f_it;
+      advance();
+      uint32_t qseq = 0;                                     // quads of all earlier units
+      for (;;) {
+        if (f_valid) fetch(nxt);
         __syncwarp();                                        // the previous iteration's reads of the tile are done
 #pragma unroll
         for (int i = 0; i < kS; ++i) ct[(2 * i + lr) * kCP + lj] = cur[i];
         __syncwarp();
-        float row[kS];
-#pragma unroll
-        for (int c = 0; c < kS / 4; ++c) {
-          const float4 v4 = *reinterpret_cast<const float4*>(ct + lane * kCP + 4 * c);
-          row[4 * c] = v4.x; row[4 * c + 1] = v4.y; row[4 * c + 2] = v4.z; row[4 * c + 3] = v4.w;
-        }
-        const int pr = kConvSets * it + set;                  // my pair of k-steps
+        const int pr = kConvSets * c_it + set;               // my pair of k-steps (phantom pairs of the padding included)
         if (pr < P.ksteps) {
-          const uint32_t psq = kseq + pr;
-          const uint32_t as = psq % kAStagesTc, ause = psq / kAStagesTc;
-          const uint32_t a_base = tmem + lane_addr + kColATc + as * 32;
           uint32_t hi[kS], lo[kS];
 #pragma unroll
-          for (int j = 0; j < kS; ++j) {
-            const uint32_t hb = __float_as_uint(row[j]) & 0xFFFFE000u;
-            hi[j] = hb;
-            lo[j] = __float_as_uint(row[j] - __uint_as_float(hb));
+          for (int c = 0; c < kS / 4; ++c) {
+            const float4 v4 = *reinterpret_cast<const float4*>(ct + lane * kCP + 4 * c);
+            const float rv[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t hb = __float_as_uint(rv[j]) & 0xFFFFE000u;
+              hi[4 * c + j] = hb;
+              lo[4 * c + j] = __float_as_uint(rv[j] - __uint_as_float(hb));
+            }
           }
+          const uint32_t qs = qseq + (uint32_t)(pr >> 1);
+          const uint32_t as = qs % kAStagesTc, ause = qs / kAStagesTc;
+          const uint32_t a_base = tmem + lane_addr + kColATc + as * 64 + (uint32_t)(pr & 1) * 32;
           mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
           tc_fence_after();
-          tmem_st8(a_base, hi);
-          tmem_st8(a_base + 8, lo);
-          tmem_st8(a_base + 16, hi + 8);
-          tmem_st8(a_base + 24, lo + 8);
-          tmem_wait_st();
+          if (!(P.exp & 256)) {
+            tmem_st8(a_base, hi);
+            tmem_st8(a_base + 8, lo);
+            tmem_st8(a_base + 16, hi + 8);
+            tmem_st8(a_base + 24, lo + 8);
+            tmem_wait_st();
+          }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
         }
+        if (!(f_valid && f_u == c_u)) qseq += (uint32_t)nquads;      // that was this unit's last iteration
+        if (!f_valid) break;
+        c_u = f_u;
+        c_it = f_it;
+        advance();
 #pragma unroll
         for (int j = 0; j < kS; ++j) cur[j] = nxt[j];
       }
-      kseq += P.ksteps;
     }
   } else if (warp >= kWarpEpiTc && !(P.exp & 4)) {
     // ===== epilogue =====
@@ -322,11 +370,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
 }
 
 inline int b_stages(int nbp) {
-  const int n = kBRingBytes / (nbp * 128);
+  const int n = kBRingBytes / (nbp * 256);
   return n > kBStagesMax ? kBStagesMax : n;
 }
 inline size_t smem_bytes(int nbp) {
-  return (size_t)b_stages(nbp) * nbp * 128 + (4 * kEpiSets * 32 * kTPitch + 4 * kConvSets * 32 * 20) * sizeof(float) +
+  return (size_t)b_stages(nbp) * nbp * 256 + (4 * kEpiSets * 32 * kTPitch + 4 * kConvSets * 32 * 20) * sizeof(float) +
          sizeof(Barriers) + 16;
 }
 
