@@ -1,5 +1,5 @@
 """Leg-removal timings of k_resample_tc (TTTS_RESAMPLE_EXP: 1 no converters, 2 no taps loads, 4 no epilogue, 32 no MMAs,
-64 no L2 prefetch, 128 converters without global loads, 256 converters without TMEM stores).
+128 converters without global loads, 256 converters without TMEM stores).
 Results are INVALID while a flag is set; this only attributes time."""
 import os, sys
 import numpy as np, torch
@@ -10,7 +10,7 @@ for o, n in ((44100, 24000), (24000, 22050), (16000, 22050)):
     x = torch.rand((64, o * 10), device="cuda") * 2 - 1
     rs = Resampler(o, n)
     line = f"{rs.orig}:{rs.new}"
-    for exp in (0, 64, 38, 38 | 128, 38 | 256, 1, 2, 4, 32, 1 | 2, 1 | 4, 2 | 4, 1 | 2 | 4, 1 | 2 | 32, 2 | 4 | 32, 1 | 2 | 4 | 32):
+    for exp in (0, 38, 38 | 128, 38 | 256, 1, 2, 4, 32, 1 | 2, 1 | 4, 2 | 4, 1 | 2 | 4, 1 | 2 | 32, 2 | 4 | 32, 1 | 2 | 4 | 32):
         os.environ["TTTS_RESAMPLE_EXP"] = str(exp)
         ms = []
         for i in range(8):

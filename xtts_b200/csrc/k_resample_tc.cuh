@@ -25,8 +25,7 @@ namespace tc {
 
 constexpr int kTileM = 128;
 constexpr int kThreadsTc = 768;        // 4 misc + 12 converter + 8 epilogue warps
-constexpr int kBStagesMax = 16;        // taps ring: as many stages as fit kBRingBytes (the MMAs of a k-step are short,
-constexpr int kBRingBytes = 160 * 1024;   // so the bulk copies' latency needs many stages in flight)
+constexpr int kBStagesMax = 4;
 constexpr int kAStagesTc = 3;          // x 64 TMEM columns: one quad of k-steps, (hi 8 | lo 8) each
 constexpr int kMaxNb = 160;            // phases per block; two accumulator buffers = 320 columns
 constexpr int kColATc = 2 * kMaxNb;    // A ring: columns 320..511
@@ -51,7 +50,7 @@ struct Params {
   long long units;            // B * tiles_per_clip * npass
   int clip;
   int b_stages;               // taps ring depth
-  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no taps loads, 4 no epilogue, 32 no MMAs, 64 no L2 prefetch
+  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no taps loads, 4 no epilogue, 32 no MMAs, 128 converters without global loads, 256 without TMEM stores
   int32_t* status;
 };
 
@@ -111,34 +110,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
   if (warp == 0) {
     // ===== taps producer =====
     if (lane == 0 && !(P.exp & 2)) {
-      // The converters read every input sample about once, straight from DRAM: what they can keep in flight (one
-      // iteration of register prefetch per warp) does not cover that latency.  The samples of the unit two rounds
-      // ahead are therefore pulled into L2 here with bulk prefetches (no registers, no shared memory).
-      auto prefetch_unit = [&](long long u) {
-        if (u >= P.units || (P.exp & 64)) return;
-        const Unit un = locate(P, u);
-        if (!un.live) return;
-        const long long esz = (long long)sizeof(TIn) * P.channels;
-        long long sa = un.row0 * P.orig - P.width, sb = (un.row0 + kTileM) * P.orig - P.width + 16LL * P.ksteps;
-        if (sa < 0) sa = 0;
-        if (sb > un.len) sb = un.len;
-        const char* base = reinterpret_cast<const char*>(P.x) + (long long)un.b * P.row_stride * (long long)sizeof(TIn);
-        uintptr_t a0 = ((uintptr_t)(base + sa * esz) + 15) & ~(uintptr_t)15;
-        const uintptr_t a1 = (uintptr_t)(base + sb * esz) & ~(uintptr_t)15;
-        for (; a0 < a1; a0 += 32768) {
-          const uint32_t n = (uint32_t)((a1 - a0) < 32768 ? (a1 - a0) : 32768);
-          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(n) : "memory");
-        }
-      };
-      prefetch_unit((long long)blockIdx.x + gridDim.x);
       uint32_t seq = 0;
       for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
-        prefetch_unit(u + 2LL * gridDim.x);
         const Unit un = locate(P, u);
         if (!un.live) continue;
         for (int ks = 0; ks < nquads; ++ks, ++seq) {
           const uint32_t st = seq % nbs, use = seq / nbs;
-          mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
+          mbar_wait(smem_u32(&bars->a_empty[st]), (use & 1) ^ 1, P.status, 101);   // one "stage free" barrier for A and B
           const uint32_t full = smem_u32(&bars->b_full[st]);
           mbar_expect_tx(full, b_stage_bytes);
           bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
@@ -181,8 +159,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
               mma_tf32_ts(d, a_hi, b_hi, idesc, 1u);
             }
           }
-          tc_commit(smem_u32(&bars->b_empty[st]));
-          tc_commit(smem_u32(&bars->a_empty[as]));
+          tc_commit(smem_u32(&bars->a_empty[as]));       // frees the A stage and the B stage (same index, same depth)
           if (ks == nquads - 1) tc_commit(smem_u32(&bars->acc_full[abuf]));
         }
         __syncwarp();
@@ -369,10 +346,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
   }
 }
 
-inline int b_stages(int nbp) {
-  const int n = kBRingBytes / (nbp * 256);
-  return n > kBStagesMax ? kBStagesMax : n;
-}
+inline int b_stages(int) { return kAStagesTc; }       // the taps ring shares the A ring's depth and "free" barrier
 inline size_t smem_bytes(int nbp) {
   return (size_t)b_stages(nbp) * nbp * 256 + (4 * kEpiSets * 32 * kTPitch + 4 * kConvSets * 32 * 20) * sizeof(float) +
          sizeof(Barriers) + 16;
