@@ -361,3 +361,16 @@ def test_gpu_kernels_stay_inside_their_rows(rates):
     torch.cuda.synchronize()
     body = buf[3:].view(B, L + 9)
     assert bool((buf[:3] == 777.0).all()) and bool((body[:, L:] == 777.0).all()) and bool((body[:, :L] != 777.0).all())
+
+
+@gpu
+def test_gpu_unreduced_or_huge_ratios_fail_loudly():
+    """Coprime rates one apart need a 44101 x 44114 tap table: the plan refuses instead of allocating gigabytes."""
+    import ctypes
+    from xtts_b200 import _cabi
+    lib = _cabi.lib()
+    h = ctypes.c_void_p()
+    taps = torch.zeros(16)
+    assert lib.ttts_resample_plan_create(taps.data_ptr(), 44100, 44101, 7, ctypes.byref(h)) == _cabi.EINVAL
+    assert b"gcd" in lib.ttts_mel_last_error()
+    assert lib.ttts_resample_plan_create(taps.data_ptr(), 0, 3, 7, ctypes.byref(h)) == _cabi.EINVAL

@@ -320,8 +320,12 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   const int kwp = (kw + 3) / 4 * 4;
   // CTA tile (k_resample): up to 32 phase quads (one warp's lanes) x as many row slots of 8 rows as fill the 256
   // threads, bounded by the staged tile (rows x kwp floats)
-  const long long max_ng = ingest::kMaxSmemFloats / kwp / ingest::kRI;
-  if (max_ng < 1) return fail(TTTS_MEL_EINVAL, "resample %d -> %d: filter too long for the staged tile", orig, new_f);
+  constexpr size_t kMaxTableBytes = (size_t)256 << 20;      // per tap table; beyond it the rates are not reduced sensibly
+  if ((size_t)kwp * new_pad * sizeof(float) > kMaxTableBytes)
+    return fail(TTTS_MEL_EINVAL, "resample %d -> %d: %d x %d taps do not fit a table (are the rates divided by their gcd?)", orig, new_f, new_f, kw);
+  long long max_ng = ingest::kMaxSmemFloats / kwp / ingest::kRI;
+  const bool simt_ok = max_ng >= 1;
+  if (!simt_ok) max_ng = 1;
   const int nq = new_pad / ingest::kRP;
   const int npb = (nq + 31) / 32;
   const int nqb = (nq + npb - 1) / npb;
@@ -343,12 +347,17 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   cudaError_t e = cudaGetDevice(&p->device);
   // tensor-core path: phases in blocks of <= 192 (multiples of 16), taps in k-steps of 8, split hi / lo
   p->tc = (new_f >= 16 && !p->decimate && !getenv("TTTS_RESAMPLE_SIMT")) ? 1 : 0;
+  p->npass = (new_f + ingest::tc::kMaxNb - 1) / ingest::tc::kMaxNb;
+  p->nbp = ((new_f + p->npass - 1) / p->npass + 15) / 16 * 16;
+  p->ksteps = (kw + 31) / 32 * 2;                     // pairs of k-steps, rounded up to whole quads
+  const size_t arr = (size_t)2 * p->nbp * 4;          // one operand array: [2 k-halves][nbp][4]
+  if ((size_t)p->npass * p->ksteps * 4 * arr * sizeof(float) > kMaxTableBytes) p->tc = 0;
+  if (!p->tc && !p->decimate && !simt_ok) {
+    delete p;
+    return fail(TTTS_MEL_EINVAL, "resample %d -> %d: filter of %d taps too long for either kernel", orig, new_f, kw);
+  }
   std::vector<float> tb;
   if (p->tc) {
-    p->npass = (new_f + ingest::tc::kMaxNb - 1) / ingest::tc::kMaxNb;
-    p->nbp = ((new_f + p->npass - 1) / p->npass + 15) / 16 * 16;
-    p->ksteps = (kw + 31) / 32 * 2;                   // pairs of k-steps, rounded up to whole quads
-    const size_t arr = (size_t)2 * p->nbp * 4;        // one operand array: [2 k-halves][nbp][4]
     tb.assign((size_t)p->npass * p->ksteps * 4 * arr, 0.f);
     for (int pb = 0; pb < p->npass; ++pb)
       for (int pr = 0; pr < p->ksteps; ++pr) {

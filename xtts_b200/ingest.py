@@ -115,6 +115,12 @@ class Resampler:
     def __init__(self, orig_freq: int, new_freq: int, *, lowpass_filter_width: int = 6, rolloff: float = 0.99,
                  kernel_dtype: Optional[torch.dtype] = torch.float32, device: Union[str, torch.device, int] = "cuda"):
         self.device = _resolve(device)
+        g = math.gcd(int(orig_freq), int(new_freq))
+        o, n = int(orig_freq) // g, int(new_freq) // g
+        w = math.ceil(lowpass_filter_width * o / (min(o, n) * rolloff))
+        if n * (2 * w + o) > (64 << 20):
+            raise ValueError(f"resample {orig_freq} -> {new_freq}: {n} phases x {2 * w + o} taps do not fit a table "
+                             "(rates that share no large common divisor are not supported)")
         taps, self.orig, self.new, self.width = sinc_resample_taps(orig_freq, new_freq, lowpass_filter_width,
                                                                    rolloff, kernel_dtype)
         self.taps = taps
