@@ -10,7 +10,8 @@ plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n
                power=2.0, norm="slaney", device=dev)
 x = torch.rand(64, 220500, device=dev) * 2 - 1
 names = {0: "full", 1: "no A handoff", 2: "no basis loads", 4: "no epilogue", 3: "MMA+epilogue only", 5: "no A, no epi",
-         6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only", 32: "no MMAs", 36: "no MMAs, no epilogue", 38: "converters only (no MMA/basis/epi)", 34: "no MMAs, no basis"}
+         6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only", 32: "no MMAs", 36: "no MMAs, no epilogue", 38: "converters only (no MMA/basis/epi)", 34: "no MMAs, no basis",
+         71: "MMA issue only, no per-k-step commits", 39: "bare issue loop (no MMAs)", 103: "bare loop, no commits"}
 FLAGS = [int(a) for a in sys.argv[1:]] or [0, 4, 8, 16, 24, 7, 32, 36, 38, 34, 0]
 for flags in FLAGS:
     lib.ttts_mel_set_experiment(flags)
@@ -23,6 +24,6 @@ for flags in FLAGS:
     buf = (ctypes.c_float * 20)()
     n = lib.ttts_mel_profile_collect(buf, 20)
     ms = sorted(buf[i] for i in range(n))
-    print(f"flags={flags} ({names[flags]:>20s}): k_logmel median {ms[n//2]*1e3:7.1f} us  min {ms[0]*1e3:7.1f} us", flush=True)
+    print(f"flags={flags} ({names.get(flags, "?"):>20s}): k_logmel median {ms[n//2]*1e3:7.1f} us  min {ms[0]*1e3:7.1f} us", flush=True)
     lib.ttts_mel_profile_enable(0)
 lib.ttts_mel_set_experiment(0)

@@ -335,8 +335,10 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
                 mma(d_im, o_hi, s_hi, 1u);
               }
             }
+            if (!(P.exp_flags & 64)) {                       // (64: timing experiment, only valid together with 1 | 2)
             commit(smem_u32(&bars->b_empty[st]));            // basis stage free once these MMAs retire
             commit(smem_u32(&bars->a_empty[as]));            // A stage free
+            }
             if (ks == kKS - 1) commit(smem_u32(&bars->acc_full));
           }
           __syncwarp();
