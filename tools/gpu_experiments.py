@@ -11,6 +11,7 @@ plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n
 x = torch.rand(64, 220500, device=dev) * 2 - 1
 names = {0: "full", 1: "no A handoff", 2: "no basis loads", 4: "no epilogue", 3: "MMA+epilogue only", 5: "no A, no epi",
          6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only", 32: "no MMAs", 36: "no MMAs, no epilogue", 38: "converters only (no MMA/basis/epi)", 34: "no MMAs, no basis",
+         35: "epilogue only", 43: "epilogue only, no drain math", 51: "epilogue only, no log pass", 59: "epilogue only: TMEM loads + barriers",
          71: "MMA issue only, no per-k-step commits", 39: "bare issue loop (no MMAs)", 103: "bare loop, no commits"}
 FLAGS = [int(a) for a in sys.argv[1:]] or [0, 4, 8, 16, 24, 7, 32, 36, 38, 34, 0]
 for flags in FLAGS:
