@@ -156,6 +156,9 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the log-mel path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from xtts_b200.hostmem import bind_to_gpu_numa, unbind
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_to_gpu_numa(local)          # before any pinned allocation: the staging buffers live next to the GPU
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -303,6 +306,7 @@ def run_ours(args):
         cpu_line = None
         if world == 1 and not args.no_cpu_baseline:
             xs = inputs[0].cpu()
+            unbind(all_cpus)                    # the CPU leg gets every core again, not just the GPU's NUMA node
             torch.set_num_threads(os.cpu_count() or 1)
             val, sec, cores = cpu_reference_throughput(12, 1, xs)
             cpu_line = {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port",
@@ -353,6 +357,7 @@ def run_ours(args):
             "e2e": {"value": e2e_val, "unit": "audio-s/s", "h2d_bytes_per_step": B_CLIPS * CLIP_LEN * 4,
                     "d2h_bytes_per_step": B_CLIPS * T * 80 * 4, "ms_per_step": e2e_s / K * 1e3,
                     "how": "TorchMelSpectrogram.forward on pinned host batches, double-buffered H2D/D2H streams, wall clock",
+                    "numa": numa,
                     "max_abs_diff_vs_resident": chk},
             "gpu_launches": launches,
             "kernels_per_step": {"k_prep(+edge buffers)": 1, "k_logmel2": 1},

@@ -155,3 +155,31 @@ def test_pcm16_corpus_sweep_matches_clip_by_clip_reference(tmp_path):
     calls = []
     sweep.run_stats(lambda idx, m: calls.append(idx), done=mel_pth_done(paths))
     assert calls == []
+
+
+def test_numa_binding_reads_sysfs_and_degrades_quietly(tmp_path, monkeypatch):
+    from xtts_b200 import hostmem
+    assert hostmem._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert hostmem._parse_cpulist("") == set()
+
+    class Props:
+        pci_domain_id, pci_bus_id, pci_device_id = 0, 0x1b, 0
+    monkeypatch.setattr(torch.cuda, "get_device_properties", lambda i: Props())
+    # no sysfs entry (VM / single socket): nothing changes
+    before = os.sched_getaffinity(0)
+    assert hostmem.bind_to_gpu_numa(0, sysfs=str(tmp_path)) == {"node": None, "cpus": len(before)}
+    d = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    d.mkdir(parents=True)
+    (d / "numa_node").write_text("-1\n")
+    assert hostmem.gpu_numa_node(0, sysfs=str(tmp_path)) is None
+    (d / "numa_node").write_text("1\n")
+    assert hostmem.gpu_numa_node(0, sysfs=str(tmp_path)) == 1
+    n = tmp_path / "devices/system/node/node1"
+    n.mkdir(parents=True)
+    keep = sorted(before)[:1]
+    (n / "cpulist").write_text(f"{keep[0]},100000\n")           # one CPU we may use, one that does not exist
+    try:
+        assert hostmem.bind_to_gpu_numa(0, sysfs=str(tmp_path)) == {"node": 1, "cpus": 1}
+        assert os.sched_getaffinity(0) == set(keep)
+    finally:
+        os.sched_setaffinity(0, before)
