@@ -173,7 +173,8 @@ def test_gpu_decode_pcm16_ragged_batch_zero_fills():
 @gpu
 @pytest.mark.parametrize("rates", [(44100, 22050), (48000, 24000), (16000, 22050), (22050, 24000), (44100, 24000),
                                    (8000, 24000), (24000, 22050), (44100, 16000), (48000, 16000), (32000, 8000),
-                                   (48000, 22050), (16000, 24000)])
+                                   (48000, 22050), (16000, 24000), (25, 16), (16, 25), (50, 33), (7, 5), (5, 7),
+                                   (1000, 999)])
 @pytest.mark.parametrize("kernel_dtype", [torch.float32, None], ids=["functional", "transform"])
 def test_gpu_resampler_matches_torchaudio_call(rates, kernel_dtype):
     """Dense batch against the reference's two call forms: functional.resample (utils.py:41) and
@@ -192,7 +193,9 @@ def test_gpu_resampler_matches_torchaudio_call(rates, kernel_dtype):
     assert y.shape == ref.shape == (3, ing.out_len(20011, o, n))
     assert np.abs(y - ref).max() <= RESAMPLE_TOL
     truth = ing.restated_resample(x, o, n)
-    assert np.abs(y - truth).max() <= TRUTH_TOL
+    # torchaudio's fp32 tap positions get coarser as the reduced rates grow (argument ~ 6 pi x cutoff): at 1000:999 its
+    # own output is 2e-4 from the exact windowed sinc, and this kernel follows torchaudio, not the truth
+    assert np.abs(y - truth).max() <= (TRUTH_TOL if max(rs.orig, rs.new) <= 441 else 10 * TRUTH_TOL)
 
 
 @gpu
