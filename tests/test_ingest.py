@@ -377,3 +377,18 @@ def test_gpu_unreduced_or_huge_ratios_fail_loudly():
     assert lib.ttts_resample_plan_create(taps.data_ptr(), 44100, 44101, 7, ctypes.byref(h)) == _cabi.EINVAL
     assert b"gcd" in lib.ttts_mel_last_error()
     assert lib.ttts_resample_plan_create(taps.data_ptr(), 0, 3, 7, ctypes.byref(h)) == _cabi.EINVAL
+
+
+@gpu
+def test_gpu_plans_of_different_sizes_coexist():
+    """A plan with few phases created after one with many must not shrink the first one's launch limits
+    (the dynamic shared-memory attribute is per kernel, not per plan)."""
+    from xtts_b200 import Resampler
+    x = torch.rand((2, 30000), device="cuda") * 2 - 1
+    big = Resampler(16000, 22050)
+    y0 = big(x)
+    small = Resampler(25, 16)
+    small(x)
+    tiny = Resampler(16000, 24000)
+    tiny(x)
+    assert torch.equal(big(x), y0)

@@ -385,7 +385,9 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
     if (e == cudaSuccess) e = cudaMemcpy(p->d_tapsB, tb.data(), tb.size() * sizeof(float), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_status, sizeof(int32_t));
     if (e == cudaSuccess) e = cudaMemset(p->d_status, 0, sizeof(int32_t));
-    const int dyn = (int)ingest::tc::smem_bytes(p->nbp);
+    // the attribute belongs to the function, not to the plan: always the largest tile, or a later plan with fewer
+    // phases would make an earlier plan's launches fail
+    const int dyn = (int)ingest::tc::smem_bytes(ingest::tc::kMaxNb);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::tc::k_resample_tc<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::tc::k_resample_tc<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
   }
