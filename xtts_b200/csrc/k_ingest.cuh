@@ -15,8 +15,14 @@ constexpr float kPcmScale = 1.0f / 32768.0f;
 
 // sample s of a clip: float32 as is, int16 -> channel 0 of frame s, scaled
 __device__ __forceinline__ float load_sample(const float* src, long long s, int) { return __ldg(src + s); }
+// int16 -> x / 32768 without the conversion pipe (I2F runs at a quarter of the ALU rate): the sample in offset
+// binary is dropped into the mantissa of 2^23, and one FMA scales and removes the offset -- exact:
+//   (2^23 + x + 32768) * 2^-15 - 257 = x / 32768
+__device__ __forceinline__ float pcm16_to_float(uint32_t low16) {
+  return fmaf(__uint_as_float(((low16 ^ 0x8000u) & 0xFFFFu) | 0x4B000000u), kPcmScale, -257.0f);
+}
 __device__ __forceinline__ float load_sample(const int16_t* src, long long s, int channels) {
-  return (float)__ldg(src + s * channels) * kPcmScale;
+  return pcm16_to_float(__ldg(reinterpret_cast<const unsigned short*>(src) + s * channels));
 }
 
 // ---------------------------------------------------------------------------------------------- k_pcm16
@@ -39,19 +45,19 @@ __global__ void __launch_bounds__(kThreads) k_pcm16(const int16_t* __restrict__ 
       const int w[4] = {s.x, s.y, s.z, s.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        v[2 * j] = (float)(short)(w[j] & 0xFFFF) * kPcmScale;
-        v[2 * j + 1] = (float)(short)(w[j] >> 16) * kPcmScale;
+        v[2 * j] = pcm16_to_float((uint32_t)w[j]);
+        v[2 * j + 1] = pcm16_to_float((uint32_t)w[j] >> 16);
       }
     } else if (f0 + 8 <= nf && vec_ok && kC == 2) {
       const int4 s0 = __ldg(reinterpret_cast<const int4*>(src + 2 * f0));       // 4 frames x (ch0, ch1)
       const int4 s1 = __ldg(reinterpret_cast<const int4*>(src + 2 * f0 + 8));
       const int w[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = (float)(short)(w[j] & 0xFFFF) * kPcmScale;
+      for (int j = 0; j < 8; ++j) v[j] = pcm16_to_float((uint32_t)w[j]);
     } else {
 #pragma unroll
       for (int j = 0; j < 8; ++j)
-        if (f0 + j < nf) v[j] = (float)src[(f0 + j) * channels] * kPcmScale;
+        if (f0 + j < nf) v[j] = load_sample(src, f0 + j, channels);
     }
     if (f0 + 8 <= frames && vec_ok) {
       reinterpret_cast<float4*>(dst + f0)[0] = make_float4(v[0], v[1], v[2], v[3]);
@@ -81,13 +87,13 @@ __device__ __forceinline__ float4 load_quad(const float* src, long long s, int, 
 __device__ __forceinline__ float4 load_quad(const int16_t* src, long long s, int channels, int vec) {
   if (vec && channels == 1) {
     const int2 w = __ldg(reinterpret_cast<const int2*>(src + s));
-    return make_float4((float)(short)(w.x & 0xFFFF) * kPcmScale, (float)(short)(w.x >> 16) * kPcmScale,
-                       (float)(short)(w.y & 0xFFFF) * kPcmScale, (float)(short)(w.y >> 16) * kPcmScale);
+    return make_float4(pcm16_to_float((uint32_t)w.x), pcm16_to_float((uint32_t)w.x >> 16),
+                       pcm16_to_float((uint32_t)w.y), pcm16_to_float((uint32_t)w.y >> 16));
   }
   if (vec && channels == 2) {
     const int4 w = __ldg(reinterpret_cast<const int4*>(src + 2 * s));
-    return make_float4((float)(short)(w.x & 0xFFFF) * kPcmScale, (float)(short)(w.y & 0xFFFF) * kPcmScale,
-                       (float)(short)(w.z & 0xFFFF) * kPcmScale, (float)(short)(w.w & 0xFFFF) * kPcmScale);
+    return make_float4(pcm16_to_float((uint32_t)w.x), pcm16_to_float((uint32_t)w.y),
+                       pcm16_to_float((uint32_t)w.z), pcm16_to_float((uint32_t)w.w));
   }
   return make_float4(load_sample(src, s, channels), load_sample(src, s + 1, channels),
                      load_sample(src, s + 2, channels), load_sample(src, s + 3, channels));

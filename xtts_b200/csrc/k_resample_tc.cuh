@@ -24,13 +24,19 @@
 namespace tc {
 
 constexpr int kTileM = 128;
-constexpr int kThreadsTc = 768;        // 4 misc + 12 converter + 8 epilogue warps
+#ifndef RTC_CONV_SETS
+#define RTC_CONV_SETS 3
+#endif
+#ifndef RTC_EPI_SETS
+#define RTC_EPI_SETS 2
+#endif
+constexpr int kConvSets = RTC_CONV_SETS, kEpiSets = RTC_EPI_SETS;
+constexpr int kThreadsTc = 32 * (4 + 4 * kConvSets + 4 * kEpiSets);   // 4 misc + 12 converter + 8 epilogue warps
 constexpr int kBStagesMax = 4;
 constexpr int kAStagesTc = 3;          // x 64 TMEM columns: one quad of k-steps, (hi 8 | lo 8) each
 constexpr int kMaxNb = 160;            // phases per block; two accumulator buffers = 320 columns
 constexpr int kColATc = 2 * kMaxNb;    // A ring: columns 320..511
-constexpr int kWarpConvTc = 4, kWarpEpiTc = 16;
-constexpr int kConvSets = 3, kEpiSets = 2;
+constexpr int kWarpConvTc = 4, kWarpEpiTc = 4 + 4 * kConvSets;
 constexpr int kTPitch = 33;            // epilogue transpose buffer pitch (floats)
 
 struct Params {
@@ -182,6 +188,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
     const int iters = (P.ksteps + kConvSets - 1) / kConvSets;      // pairs per set, rounded up
     const int lj = lane & 15, lr = lane >> 4;
     const long long rstep = 2LL * P.orig * P.channels;             // elements between the rows of consecutive loads
+    const bool stereo32 = P.channels == 2 && ((uintptr_t)P.x & 3) == 0 && (P.row_stride & 1) == 0;
     // fetch cursor: the (unit, iteration) whose samples are loaded next; it runs one iteration ahead of the consume
     // cursor and crosses unit boundaries, so the load pipeline never drains between units
     long long f_u = blockIdx.x, f_sl = 0, f_len = 0;
@@ -202,26 +209,36 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
       }
     };
     auto advance = [&]() { if (++f_it >= iters) enter(f_u + gridDim.x); };
-    auto fetch = [&](float (&v)[kS]) {
+    // the prefetch registers hold the raw words (float bits, or the 16-bit sample zero-extended); int16 samples are
+    // converted when they are written to the tile, so that the 16 loads of an iteration are issued back to back
+    auto raw_load = [&](const TIn* p) -> uint32_t {
+      if (sizeof(TIn) == 4) return __float_as_uint(__ldg(reinterpret_cast<const float*>(p)));
+      if (stereo32) return (uint32_t)__ldg(reinterpret_cast<const int*>(p));         // frame = (ch0 | ch1 << 16)
+      return (uint32_t)__ldg(reinterpret_cast<const unsigned short*>(p));
+    };
+    auto to_float = [&](uint32_t w) -> float {
+      return sizeof(TIn) == 4 ? __uint_as_float(w) : pcm16_to_float(w);
+    };
+    auto fetch = [&](uint32_t (&v)[kS]) {
       const int k0 = kS * (kConvSets * f_it + set);
       const TIn* pk = f_lp + (long long)k0 * P.channels;
       if (P.exp & 128) {
 #pragma unroll
-        for (int i = 0; i < kS; ++i) v[i] = 0.25f * i;
+        for (int i = 0; i < kS; ++i) v[i] = 0u;
       } else if (f_interior) {
 #pragma unroll
-        for (int i = 0; i < kS; ++i) v[i] = load_sample(pk + i * rstep, 0, 1);
+        for (int i = 0; i < kS; ++i) v[i] = raw_load(pk + i * rstep);
       } else {
 #pragma unroll
         for (int i = 0; i < kS; ++i) {
           const long long sj = f_sl + k0 + 2LL * i * P.orig;
-          v[i] = (sj >= 0 && sj < f_len) ? load_sample(pk + i * rstep, 0, 1) : 0.f;
+          v[i] = (sj >= 0 && sj < f_len) ? raw_load(pk + i * rstep) : 0u;          // raw 0 is 0.0 in both encodings
         }
       }
     };
     enter(blockIdx.x);
     if (f_valid) {
-      float cur[kS], nxt[kS];
+      uint32_t cur[kS], nxt[kS];
       fetch(cur);
       long long c_u = f_u;
       int c_it = f_it;
@@ -231,7 +248,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_resample_tc(const Params P) {
         if (f_valid) fetch(nxt);
         __syncwarp();                                        // the previous iteration's reads of the tile are done
 #pragma unroll
-        for (int i = 0; i < kS; ++i) ct[(2 * i + lr) * kCP + lj] = cur[i];
+        for (int i = 0; i < kS; ++i) ct[(2 * i + lr) * kCP + lj] = to_float(cur[i]);
         __syncwarp();
         const int pr = kConvSets * c_it + set;               // my pair of k-steps (phantom pairs of the padding included)
         if (pr < P.ksteps) {
