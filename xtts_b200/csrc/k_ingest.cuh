@@ -79,24 +79,27 @@ constexpr int kDecTile = kThreads * kDecR;
 // neighbour's, and the padding spreads the 16-byte chunks of 8 neighbouring lanes over distinct banks
 __device__ __forceinline__ int dec_pad(int i) { return i + ((i >> 4) << 2); }
 
-// four consecutive samples s .. s+3 (s % 4 == 0, all inside the clip, row base suitably aligned: `vec`)
-__device__ __forceinline__ float4 load_quad(const float* src, long long s, int, int vec) {
-  if (vec) return __ldg(reinterpret_cast<const float4*>(src + s));
-  return make_float4(__ldg(src + s), __ldg(src + s + 1), __ldg(src + s + 2), __ldg(src + s + 3));
+// four consecutive samples s .. s+3 (s % 4 == 0, all inside the clip, row base suitably aligned), split in a raw
+// 16-byte load and a conversion so that a thread can issue all its loads before it touches the first result
+__device__ __forceinline__ int4 raw_quad(const float* src, long long s, int) {
+  return __ldg(reinterpret_cast<const int4*>(src + s));
 }
-__device__ __forceinline__ float4 load_quad(const int16_t* src, long long s, int channels, int vec) {
-  if (vec && channels == 1) {
+__device__ __forceinline__ int4 raw_quad(const int16_t* src, long long s, int channels) {
+  if (channels == 1) {
     const int2 w = __ldg(reinterpret_cast<const int2*>(src + s));
+    return make_int4(w.x, w.y, 0, 0);
+  }
+  return __ldg(reinterpret_cast<const int4*>(src + 2 * s));          // channels == 2: 4 frames x (ch0, ch1)
+}
+__device__ __forceinline__ float4 quad_to_float(const float*, int4 w, int) {
+  return make_float4(__int_as_float(w.x), __int_as_float(w.y), __int_as_float(w.z), __int_as_float(w.w));
+}
+__device__ __forceinline__ float4 quad_to_float(const int16_t*, int4 w, int channels) {
+  if (channels == 1)
     return make_float4(pcm16_to_float((uint32_t)w.x), pcm16_to_float((uint32_t)w.x >> 16),
                        pcm16_to_float((uint32_t)w.y), pcm16_to_float((uint32_t)w.y >> 16));
-  }
-  if (vec && channels == 2) {
-    const int4 w = __ldg(reinterpret_cast<const int4*>(src + 2 * s));
-    return make_float4(pcm16_to_float((uint32_t)w.x), pcm16_to_float((uint32_t)w.y),
-                       pcm16_to_float((uint32_t)w.z), pcm16_to_float((uint32_t)w.w));
-  }
-  return make_float4(load_sample(src, s, channels), load_sample(src, s + 1, channels),
-                     load_sample(src, s + 2, channels), load_sample(src, s + 3, channels));
+  return make_float4(pcm16_to_float((uint32_t)w.x), pcm16_to_float((uint32_t)w.y),
+                     pcm16_to_float((uint32_t)w.z), pcm16_to_float((uint32_t)w.w));
 }
 
 // new == 1: out[j] = sum_k xpad[j * ORIG + k] * taps[k].  One CTA = 2048 consecutive outputs of one clip: the
@@ -127,11 +130,23 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
   }
   const TIn* src = x + (long long)b * row_stride;
   const long long s0 = j0 * ORIG - kWidth - kOff;          // multiple of 4 (negative for the first tile)
-  for (int q = threadIdx.x; q < kSeg / 4; q += kThreads) {
+  constexpr int kQuads = kSeg / 4, kIt = (kQuads + kThreads - 1) / kThreads;
+  int4 raw[kIt];
+#pragma unroll
+  for (int it = 0; it < kIt; ++it) {                        // all the 16-byte loads first ...
+    const int q = threadIdx.x + it * kThreads;
     const long long s = s0 + 4 * q;
+    raw[it] = make_int4(0, 0, 0, 0);
+    if (vec && q < kQuads && s >= 0 && s + 4 <= len) raw[it] = raw_quad(src, s, channels);
+  }
+#pragma unroll
+  for (int it = 0; it < kIt; ++it) {                        // ... then conversion and the padded stores
+    const int q = threadIdx.x + it * kThreads;
+    const long long s = s0 + 4 * q;
+    if (q >= kQuads) break;
     float4 v;
-    if (s >= 0 && s + 4 <= len) {
-      v = load_quad(src, s, channels, vec);
+    if (vec && s >= 0 && s + 4 <= len) {
+      v = quad_to_float(src, raw[it], channels);
     } else {
       v.x = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
       v.y = (s + 1 >= 0 && s + 1 < len) ? load_sample(src, s + 1, channels) : 0.f;
