@@ -19,7 +19,8 @@ def med(fn, reps=10):
         if i >= 2: ms.append(a.elapsed_time(b) / reps)
     return np.median(ms) * 1e3
 line = ""
-for o, n in ((44100, 24000), (24000, 22050), (16000, 22050), (48000, 22050)):
+RATES = [tuple(int(v) for v in a.split(':')) for a in sys.argv[1:]] or [(44100, 24000), (24000, 22050), (16000, 22050), (48000, 22050)]
+for o, n in RATES:
     x = torch.rand((64, o * 10), device="cuda") * 2 - 1
     pcm = torch.randint(-32768, 32767, (64, o * 10, 2), dtype=torch.int16, device="cuda")
     rs = Resampler(o, n)

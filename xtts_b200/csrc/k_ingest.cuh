@@ -2,7 +2,8 @@
 //   k_pcm16      interleaved int16 PCM -> float32 channel 0 (x / 32768)        HBM-bound: 2 C + 4 bytes per frame
 //   k_decimate   integer-ratio (2:1, 3:1, 4:1) windowed-sinc FIR, one phase     HBM-bound: 4 (or 2 C) ORIG + 4 bytes per output
 //   k_resample_tc general polyphase windowed-sinc FIR (orig -> new, >= 16 phases) on tcgen05 (k_resample_tc.cuh)
-//   k_resample   the same on the FMA pipe (few phases)                          FMA-bound: 2 (2 width + orig) flop per output
+//   k_resample_few  fewer than 16 phases (2:3, 1:3, 4:3, 6:1 ...): flat staged segment, one output per thread
+//   k_resample   many phases on the FMA pipe (fallback of k_resample_tc)        FMA-bound: 2 (2 width + orig) flop per output
 // The two FIR kernels read float32 or (fused decode) interleaved int16 PCM.
 // Reference: load_audio (ttts/utils/utils.py:32-47), mel_extract.py:15-21.  Included at the end of ttts_mel.cu
 // (one shared library); uses its fail() / CUDA_TRY / g_launches.
@@ -289,6 +290,61 @@ __global__ void __launch_bounds__(kThreads) k_resample(const TIn* __restrict__ x
   }
 }
 
+// ---------------------------------------------------------------------------------------------- k_resample_few
+// Few phases (new < 16: 2:3, 1:3, 4:3, 3:2, 6:1 ...): the rows overlap almost completely (kw >> orig), so the tile of
+// k_resample -- one staged copy of the taps' worth of samples per row -- would stage every sample kw / orig times.
+// Here one CTA stages the contiguous segment its `rows` strides need once (coalesced) plus the whole tap table, and
+// a thread computes one output (consecutive threads = consecutive outputs: coalesced stores; the lanes of a warp
+// read shared-memory words at most `orig` apart).
+template <typename TIn>
+__global__ void __launch_bounds__(kThreads) k_resample_few(const TIn* __restrict__ x, long long row_stride, int channels,
+                                                           const long long* __restrict__ lengths, long long L,
+                                                           const float* __restrict__ taps, int orig, int new_f,
+                                                           int width, int kw, int rows, float* __restrict__ out,
+                                                           long long out_stride, long long out_cols, int clip) {
+  extern __shared__ __align__(16) float fs[];
+  const int b = blockIdx.y;
+  const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
+  const long long olen = (len * new_f + orig - 1) / orig;
+  const long long row0 = (long long)blockIdx.x * rows;
+  const long long j0 = row0 * new_f;
+  if (j0 >= out_cols) return;
+  float* dst = out + (long long)b * out_stride + j0;
+  const int nout = (int)min((long long)rows * new_f, out_cols - j0);
+  if (j0 >= olen) {
+    for (int j = threadIdx.x; j < nout; j += kThreads) dst[j] = 0.f;
+    return;
+  }
+  const int seg = (rows - 1) * orig + kw;
+  float* xs = fs;
+  float* tp = fs + ((seg + 3) & ~3);
+  const TIn* src = x + (long long)b * row_stride;
+  const long long s0 = row0 * orig - width;
+  for (int i = threadIdx.x; i < seg; i += kThreads) {
+    const long long s = s0 + i;
+    xs[i] = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
+  }
+  for (int i = threadIdx.x; i < new_f * kw; i += kThreads) tp[i] = __ldg(taps + i);
+  __syncthreads();
+  const long long keep = olen - j0;
+  for (int jl = threadIdx.x; jl < nout; jl += kThreads) {
+    const int i = jl / new_f, p = jl - i * new_f;
+    const float* xr = xs + i * orig;
+    const float* t = tp + p * kw;
+    float a0 = 0.f, a1 = 0.f;
+    int k = 0;
+#pragma unroll 4
+    for (; k + 1 < kw; k += 2) {
+      a0 = fmaf(xr[k], t[k], a0);
+      a1 = fmaf(xr[k + 1], t[k + 1], a1);
+    }
+    if (k < kw) a0 = fmaf(xr[k], t[k], a0);
+    float v = jl < keep ? a0 + a1 : 0.f;
+    if (clip) v = fminf(fmaxf(v, -1.f), 1.f);
+    dst[jl] = v;
+  }
+}
+
 #include "k_resample_tc.cuh"
 
 }  // namespace ingest
@@ -304,6 +360,9 @@ struct ttts_resample_plan {
   int device = 0;
   float* d_tapsT = nullptr;   // [kwp][new_pad], taps and phases zero-padded to multiples of 4
   ingest::TapsParam taps1;    // the single phase of a decimator
+  int few = 0;                // k_resample_few applies (< 16 phases, not a templated decimator)
+  int few_rows = 0;           // ... input strides per CTA
+  float* d_taps = nullptr;    // ... [new_f][kw], the host layout
   int tc = 0;                 // k_resample_tc applies (>= 16 phases; TTTS_RESAMPLE_SIMT=1 forces k_resample)
   int ksteps = 0, npass = 0, nbp = 0, num_sms = 0;
   float* d_tapsB = nullptr;   // [npass][ksteps][hi | lo][2 k-halves][nbp][4] TF32-exact hi, remainder lo
@@ -373,9 +432,17 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   p->ksteps = (kw + 31) / 32 * 2;                     // pairs of k-steps, rounded up to whole quads
   const size_t arr = (size_t)2 * p->nbp * 4;          // one operand array: [2 k-halves][nbp][4]
   if ((size_t)p->npass * p->ksteps * 4 * arr * sizeof(float) > kMaxTableBytes) p->tc = 0;
-  if (!p->tc && !p->decimate && !simt_ok) {
+  p->few = (!p->tc && !p->decimate && new_f < 16 && !getenv("TTTS_RESAMPLE_SIMT") &&
+            (long long)new_f * kw + kw + orig <= ingest::kMaxSmemFloats) ? 1 : 0;
+  if (p->few) {
+    long long fr = 2048 / new_f, cap = (ingest::kMaxSmemFloats - (long long)new_f * kw - kw - 4) / orig + 1;
+    if (fr > cap) fr = cap;
+    if (fr < 1) fr = 1;
+    p->few_rows = (int)fr;
+  }
+  if (!p->tc && !p->decimate && !p->few && !simt_ok) {
     delete p;
-    return fail(TTTS_MEL_EINVAL, "resample %d -> %d: filter of %d taps too long for either kernel", orig, new_f, kw);
+    return fail(TTTS_MEL_EINVAL, "resample %d -> %d: filter of %d taps too long for any kernel", orig, new_f, kw);
   }
   std::vector<float> tb;
   if (p->tc) {
@@ -412,6 +479,12 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::tc::k_resample_tc<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::tc::k_resample_tc<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
   }
+  if (p->few) {
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_taps, (size_t)new_f * kw * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_taps, taps, (size_t)new_f * kw * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::k_resample_few<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (ingest::kMaxSmemFloats + 8) * 4);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ingest::k_resample_few<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (ingest::kMaxSmemFloats + 8) * 4);
+  }
   if (e == cudaSuccess) e = cudaMalloc(&p->d_tapsT, t.size() * sizeof(float));
   if (e == cudaSuccess) e = cudaMemcpy(p->d_tapsT, t.data(), t.size() * sizeof(float), cudaMemcpyHostToDevice);
   if (e == cudaSuccess)
@@ -431,6 +504,7 @@ extern "C" void ttts_resample_plan_destroy(ttts_resample_plan* p) {
   if (!p) return;
   cudaFree(p->d_tapsT);
   cudaFree(p->d_tapsB);
+  cudaFree(p->d_taps);
   cudaFree(p->d_status);
   delete p;
 }
@@ -470,6 +544,16 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     else if (p->orig == 3) TTTS_DEC(3, 41);
     else TTTS_DEC(4, 54);
 #undef TTTS_DEC
+  } else if (p->few) {
+    const long long tile = (long long)p->few_rows * p->new_f;
+    const long long gx = (out_cols + tile - 1) / tile;
+    if (gx > 0x7FFFFFFFLL) return fail(TTTS_MEL_EINVAL, "clip too long");
+    const int seg = (p->few_rows - 1) * p->orig + p->kw;
+    const size_t smem = ((size_t)((seg + 3) & ~3) + (size_t)p->new_f * p->kw) * sizeof(float);
+    dim3 grid((unsigned)gx, (unsigned)B);
+    ingest::k_resample_few<TIn><<<grid, ingest::kThreads, smem, st>>>(
+        x, row_stride, channels, len, L, p->d_taps, p->orig, p->new_f, p->width, p->kw, p->few_rows, out, out_stride,
+        out_cols, clip);
   } else if (p->tc) {
     ingest::tc::Params q;
     q.x = x; q.row_stride = row_stride; q.channels = channels; q.lengths = len; q.L = L; q.B = B;
