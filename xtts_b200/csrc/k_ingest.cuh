@@ -107,7 +107,7 @@ __device__ __forceinline__ float4 quad_to_float(const int16_t*, int4 w, int chan
 // segment is staged once in shared memory (16-byte loads and stores: it starts at the multiple of 4 at or below
 // the first sample the tile needs, kOff samples early), each thread pulls the samples its 8 outputs share into
 // registers with 16-byte loads, and the R x KW FMAs take their taps from the kernel-parameter constant bank.
-template <int ORIG, int KW, typename TIn>
+template <int ORIG, int KW, typename TIn, bool kHoist>
 __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x, long long row_stride, int channels,
                                                        const long long* __restrict__ lengths, long long L,
                                                        const TapsParam taps, float* __restrict__ out,
@@ -132,13 +132,14 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
   const TIn* src = x + (long long)b * row_stride;
   const long long s0 = j0 * ORIG - kWidth - kOff;          // multiple of 4 (negative for the first tile)
   constexpr int kQuads = kSeg / 4, kIt = (kQuads + kThreads - 1) / kThreads;
+
   int4 raw[kIt];
 #pragma unroll
   for (int it = 0; it < kIt; ++it) {                        // all the 16-byte loads first ...
     const int q = threadIdx.x + it * kThreads;
     const long long s = s0 + 4 * q;
     raw[it] = make_int4(0, 0, 0, 0);
-    if (vec && q < kQuads && s >= 0 && s + 4 <= len) raw[it] = raw_quad(src, s, channels);
+    if (kHoist && vec && q < kQuads && s >= 0 && s + 4 <= len) raw[it] = raw_quad(src, s, channels);
   }
 #pragma unroll
   for (int it = 0; it < kIt; ++it) {                        // ... then conversion and the padded stores
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
     if (q >= kQuads) break;
     float4 v;
     if (vec && s >= 0 && s + 4 <= len) {
-      v = quad_to_float(src, raw[it], channels);
+      v = quad_to_float(src, kHoist ? raw[it] : raw_quad(src, s, channels), channels);
     } else {
       v.x = (s >= 0 && s < len) ? load_sample(src, s, channels) : 0.f;
       v.y = (s + 1 >= 0 && s + 1 < len) ? load_sample(src, s + 1, channels) : 0.f;
@@ -538,8 +539,14 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     const int64_t unit = sizeof(TIn) == 4 ? 4 : (channels == 2 ? 8 : 4);
     const uintptr_t align = sizeof(TIn) == 4 ? 16 : (channels == 2 ? 16 : 8);
     const int vec = (sizeof(TIn) == 4 || channels <= 2) && row_stride % unit == 0 && (uintptr_t)x % align == 0;
-#define TTTS_DEC(O, K) ingest::k_decimate<O, K, TIn><<<grid, ingest::kThreads, 0, st>>>( \
-        x, row_stride, channels, len, L, p->taps1, out, out_stride, out_cols, clip, vec)
+    // all staging loads before the first conversion pays for fp32 and mono PCM; for stereo PCM (two 16-byte loads'
+    // worth of raw words per quad of samples) the registers it takes cost more occupancy than the overlap wins
+    const bool hoist = sizeof(TIn) == 4 || channels == 1;
+#define TTTS_DEC(O, K) do { \
+      if (hoist) ingest::k_decimate<O, K, TIn, true><<<grid, ingest::kThreads, 0, st>>>( \
+          x, row_stride, channels, len, L, p->taps1, out, out_stride, out_cols, clip, vec); \
+      else ingest::k_decimate<O, K, TIn, false><<<grid, ingest::kThreads, 0, st>>>( \
+          x, row_stride, channels, len, L, p->taps1, out, out_stride, out_cols, clip, vec); } while (0)
     if (p->orig == 2) TTTS_DEC(2, 28);
     else if (p->orig == 3) TTTS_DEC(3, 41);
     else TTTS_DEC(4, 54);
