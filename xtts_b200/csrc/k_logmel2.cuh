@@ -41,7 +41,17 @@ constexpr int kWarpEpi02 = kWarpConv02 + kConvWarps2;
 constexpr int kEpiWarps = 4 * 4;                   // 4 lane quarters x kChains scan chains
 constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
 // registers per thread by role (setmaxnreg, per warpgroup): 128*40 + 384*96 + 512*40 = 62464 <= 65536; launch value 64
-constexpr int kRegsMisc = 40, kRegsConv = 96, kRegsEpi = 40;
+#ifndef F2_REGS_MISC
+#define F2_REGS_MISC 40
+#endif
+#ifndef F2_REGS_CONV
+#define F2_REGS_CONV 96
+#endif
+#ifndef F2_REGS_EPI
+#define F2_REGS_EPI 40
+#endif
+constexpr int kRegsMisc = F2_REGS_MISC, kRegsConv = F2_REGS_CONV, kRegsEpi = F2_REGS_EPI;
+static_assert(128 * kRegsMisc + 384 * kRegsConv + 512 * kRegsEpi <= 65536, "register budgets exceed the file");
 constexpr int kBStages2 = 4;                      // basis ring depth (single CTA: 4 x 24 KB)
 constexpr int kBStagesPair = 8;                   // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
 constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
