@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _header_symbols():
     names = set()
-    for h in ("ttts_mel.h", "ttts_ingest.h"):
+    for h in ("ttts_mel.h", "ttts_ingest.h", "ttts_vq.h"):
         src = open(os.path.join(ROOT, "include", h)).read()
         src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
         names |= set(re.findall(r"\b(ttts_[a-z0-9_]+)\s*\(", src))

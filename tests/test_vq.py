@@ -1,0 +1,224 @@
+"""DVAE codebook search behind the log-mel path: Quantize.forward in eval mode + embed_code.
+
+CPU part: the oracle against the golden vectors minted from the reference's ``Quantize``
+(oracle/gen_golden_vq.py), the acceptance rule on the reference's own indices, host-mirror behaviour.
+GPU part (``-m gpu``): the tcgen05 kernel through the C ABI against the goldens and the oracle.
+
+Bars: indices are integer work, but the reference's fp32 distances are rounded at ulp(|z|^2 + |e|^2) and its sgemm's
+summation order is not specified, so "identical" is defined by ``vq_oracle.check_indices``: the chosen code's exact
+(fp64) distance lies within 8 fp32 ulps of the exact minimum, and the index EQUALS the exact arg-min wherever the
+runner-up is further away than that; exact ties resolve to the lowest index.  On every committed golden case that
+rule leaves no freedom (all rows are clear or exact ties), so there the indices are compared bit for bit.
+quantize: bit-exact given equal indices (a gather and two fp32 operations).  diff: 1e-6 relative (fp32 mean).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import vq_oracle as vo
+from oracle.gen_golden_vq import CASES
+
+DIFF_RTOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    return np.load(os.path.join(golden_dir, "vq_quantize.npz"))
+
+
+def _inputs(name):
+    dim, n_embed, cs, dup, rows, ts, kind, shape = CASES[name]
+    embed = vo.synth_codebook(dim, n_embed, cs, dup)
+    z = vo.synth_tokens(rows, embed, ts, kind).reshape(shape)
+    return embed, z
+
+
+# ------------------------------------------------------------------------------------------------ CPU
+@pytest.mark.parametrize("name", list(CASES))
+def test_callsite_oracle_reproduces_reference_quantize(gold, name):
+    embed, z = _inputs(name)
+    quantize, diff, ind = vo.callsite_quantize(z, embed)
+    assert np.array_equal(ind.numpy().astype(np.int32), gold[f"{name}.embed_ind"])
+    assert abs(float(diff) - float(gold[f"{name}.diff"])) <= DIFF_RTOL * float(gold[f"{name}.diff"])
+    assert abs(quantize.double().sum().item() - float(gold[f"{name}.quantize_sum"])) <= 1e-9 * max(1.0, abs(float(gold[f"{name}.quantize_sum"])))
+    if f"{name}.quantize" in gold:
+        assert np.array_equal(quantize.numpy(), gold[f"{name}.quantize"])
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_acceptance_rule_holds_for_the_references_own_indices(gold, name):
+    embed, z = _inputs(name)
+    st = vo.check_indices(gold[f"{name}.embed_ind"], z, embed)
+    assert st["bad"] == 0 and st["rows"] == CASES[name][4]
+    # the fp64 arg-min is the reference's index on every golden row (clear winner, or exact tie -> lowest index)
+    assert st["differs_from_exact_argmin"] == 0
+
+
+def test_acceptance_rule_rejects_wrong_indices(gold):
+    embed, z = _inputs("small_near")
+    ind = gold["small_near.embed_ind"].copy().reshape(-1)
+    ind[5] = (ind[5] + 1) % embed.shape[1]
+    ind[17] = -1
+    assert vo.check_indices(ind, z, embed)["bad"] >= 2
+
+
+def test_exact_ties_resolve_to_the_lowest_index(gold):
+    embed, z = _inputs("small_ties")
+    ind = gold["small_ties.embed_ind"].reshape(-1)
+    n_embed = embed.shape[1]
+    dup_hi = {n_embed - 1 - i: (7 * i + 3) % (n_embed // 2) for i in range(8)}
+    assert not set(ind.tolist()) & set(dup_hi)            # never the higher copy
+    assert set(ind.tolist()) & set(dup_hi.values())       # and some rows do hit a duplicated code
+
+
+def test_host_mirror_interface_and_refusals(built_lib):
+    from xtts_b200.vq import Quantize, get_codebook_indices
+    q = Quantize(64, 512)
+    assert q.embed.shape == (64, 512) and q.cluster_size.shape == (512,) and q.embed_avg.shape == (64, 512)
+    assert set(dict(q.named_buffers())) == {"embed", "cluster_size", "embed_avg"}      # same state_dict keys
+    with pytest.raises(NotImplementedError, match="eval mode"):
+        q(torch.zeros(4, 64))
+    q.eval()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        q(torch.zeros(4, 64))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        q.embed_code(torch.zeros(4, dtype=torch.long))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        get_codebook_indices(q, torch.zeros(1, 4, 64))
+    with pytest.raises(NotImplementedError):
+        Quantize(64, 512, balancing_heuristic=True).eval()(torch.zeros(4, 64))
+
+
+def test_c_abi_argument_checks_without_a_gpu(built_lib):
+    import ctypes
+    h = ctypes.c_void_p()
+    e = np.zeros((4, 64), np.float32)
+    assert built_lib.ttts_vq_plan_create(None, 4, 64, ctypes.byref(h)) < 0
+    assert built_lib.ttts_vq_plan_create(e.ctypes.data, 0, 64, ctypes.byref(h)) < 0
+    assert built_lib.ttts_vq_plan_create(e.ctypes.data, 4, 8, ctypes.byref(h)) < 0
+    assert b"n_embed" in built_lib.ttts_mel_last_error()
+    assert built_lib.ttts_vq_workspace_bytes(None, 100) == 0
+    assert built_lib.ttts_vq_nearest(None, None, 0, 0, None, None, None, None, 0, None) < 0
+    built_lib.ttts_vq_plan_destroy(None)
+
+
+# ------------------------------------------------------------------------------------------------ GPU
+def _module(embed, **kw):
+    from xtts_b200.vq import Quantize
+    q = Quantize(embed.shape[0], embed.shape[1], **kw)
+    q.embed.copy_(torch.from_numpy(embed))
+    return q.eval().cuda()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(CASES))
+def test_gpu_quantize_matches_reference_golden(gold, name):
+    embed, z = _inputs(name)
+    q = _module(embed)
+    zc = torch.from_numpy(z).cuda()
+    quantize, diff, ind = q(zc)
+    q.plan(zc.device).status()
+    assert ind.dtype == torch.int64 and ind.shape == z.shape[:-1] and quantize.shape == z.shape
+    assert np.array_equal(ind.cpu().numpy().astype(np.int32), gold[f"{name}.embed_ind"])
+    g = float(gold[f"{name}.diff"])
+    assert abs(float(diff) - g) <= DIFF_RTOL * g
+    ref_q, _, _ = vo.callsite_quantize(z, embed)
+    assert torch.equal(quantize.cpu(), ref_q)              # input + (code - input), bit for bit
+    code = q.embed_code(ind)
+    assert torch.equal(code.cpu(), torch.from_numpy(embed.T[gold[f"{name}.embed_ind"].astype(np.int64)]))
+    assert abs(code.double().sum().item() - float(gold[f"{name}.code_sum"])) <= 1e-9 * max(1.0, abs(float(gold[f"{name}.code_sum"])))
+
+
+@pytest.mark.gpu
+def test_gpu_new_return_order_and_indices_only():
+    from xtts_b200.vq import get_codebook_indices
+    embed, z = _inputs("small_near")
+    q = _module(embed, new_return_order=True)
+    zc = torch.from_numpy(z).cuda()
+    quantize, ind, diff = q(zc)
+    assert ind.dtype == torch.int64 and diff.dim() == 0
+    assert torch.equal(get_codebook_indices(q, zc), ind)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,rows", [("near", 1), ("near", 127), ("near", 129), ("randn", 1000), ("tiny", 300),
+                                       ("huge", 300), ("exact", 300)])
+def test_gpu_indices_against_oracle_small_codebooks(kind, rows):
+    """Ragged row counts (partial tiles), scales, codebooks that are not a multiple of the code block."""
+    for dim, n_embed in ((64, 512), (48, 200), (100, 16), (512, 1024)):
+        embed = vo.synth_codebook(dim, n_embed, 100 + dim, duplicates=4 if kind == "exact" else 0)
+        z = vo.synth_tokens(rows, embed, 7 * rows + dim, kind)
+        q = _module(embed)
+        _, _, ind = q(torch.from_numpy(z).cuda())
+        q.plan(torch.device("cuda", 0)).status()
+        st = vo.check_indices(ind.cpu().numpy(), z, embed)
+        assert st["bad"] == 0, (dim, n_embed, st)
+        _, _, ref = vo.callsite_quantize(z, embed)
+        # both index sets obey the rule, so they can only differ on rows whose runner-up lies within the slack
+        # (codebook-independent rows at dim 512: a fraction of a percent); a wrong kernel would be far below
+        agree = float((ref == ind.cpu()).float().mean())
+        assert agree >= (0.995 if kind in ("near", "exact") else 0.98), (dim, n_embed, agree)
+        if kind == "exact":
+            assert torch.equal(ref, ind.cpu())            # exact ties: the lowest index, like the reference
+
+
+@pytest.mark.gpu
+def test_gpu_full_size_batch_properties():
+    """BASELINE config 2 behind the DVAE encoder: 64 clips x 10 s -> 64 x 216 tokens of dim 512 against 8192 codes.
+    Checked on a sample by the oracle; on the whole batch by properties: permutation equivariance, batch-split
+    invariance, run-to-run determinism, and a code scored against itself returns itself."""
+    embed = vo.synth_codebook(vo.DVAE_DIM, vo.DVAE_N_EMBED, 41)
+    rows = 64 * 216
+    z = vo.synth_tokens(rows, embed, 77, "near")
+    q = _module(embed)
+    zc = torch.from_numpy(z).cuda()
+    _, diff, ind = q(zc)
+    q.plan(zc.device).status()
+    sample = np.random.RandomState(5).choice(rows, 1024, replace=False)
+    st = vo.check_indices(ind.cpu().numpy()[sample], z[sample], embed)
+    assert st["bad"] == 0, st
+    _, _, ind2 = q(zc)
+    assert torch.equal(ind, ind2)
+    perm = torch.randperm(rows, generator=torch.Generator().manual_seed(3)).cuda()
+    _, _, indp = q(zc[perm])
+    assert torch.equal(indp, ind[perm])
+    _, _, inda = q(zc[:5000])
+    _, _, indb = q(zc[5000:])
+    assert torch.equal(torch.cat([inda, indb]), ind)
+    codes = torch.from_numpy(np.ascontiguousarray(embed.T)).cuda()
+    _, d0, self_ind = q(codes)
+    assert torch.equal(self_ind.cpu(), torch.arange(vo.DVAE_N_EMBED)) and float(d0) == 0.0
+    # diff against an fp64 evaluation with the returned indices
+    e_sel = embed.T[ind.cpu().numpy()].astype(np.float64)
+    want = float(((e_sel - z.astype(np.float64)) ** 2).mean())
+    assert abs(float(diff) - want) <= 1e-5 * want
+
+
+@pytest.mark.gpu
+def test_gpu_strided_rows_nan_rows_and_streams():
+    embed = vo.synth_codebook(64, 512, 11)
+    z = vo.synth_tokens(400, embed, 9, "near")
+    q = _module(embed)
+    plan = q.plan(torch.device("cuda", 0))
+    wide = torch.zeros(400, 72, device="cuda")
+    wide[:, :64] = torch.from_numpy(z).cuda()
+    ind_w = plan.nearest(wide[:, :64])[0]                  # row stride 72, no copy
+    ind_c = plan.nearest(torch.from_numpy(z).cuda())[0]
+    assert torch.equal(ind_w, ind_c)
+    zn = torch.from_numpy(z).cuda().clone()
+    zn[7, 3] = float("nan")
+    ind_n = plan.nearest(zn)[0]
+    assert int(ind_n[7]) == 0                              # torch.max over NaNs returns the first
+    keep = torch.ones(400, dtype=torch.bool)
+    keep[7] = False
+    assert torch.equal(ind_n.cpu()[keep], ind_c.cpu()[keep])
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        ind_s = plan.nearest(torch.from_numpy(z).cuda())[0]
+    s.synchronize()
+    assert torch.equal(ind_s, ind_c)
+    with pytest.raises(Exception):
+        q.embed_code(torch.tensor([0, 512], device="cuda"))
+        plan.status()

@@ -1,4 +1,4 @@
-"""ctypes binding of the C ABI in ``include/ttts_mel.h`` and ``include/ttts_ingest.h`` (``libttts_mel.so``, built in-tree).
+"""ctypes binding of the C ABI in ``include/ttts_mel.h``, ``include/ttts_ingest.h`` and ``include/ttts_vq.h`` (``libttts_mel.so``, built in-tree).
 
 There is no CPU implementation behind this module: if the shared library is missing or a call
 fails, an exception is raised.
@@ -57,6 +57,14 @@ SYMBOLS = {
                                              c_int64, c_int32, c_void_p]),
     "ttts_resample_pcm16_forward": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_int32, c_int64,
                                                    c_void_p, c_int64, c_int32, c_void_p]),
+    # include/ttts_vq.h
+    "ttts_vq_plan_create": (ctypes.c_int, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
+    "ttts_vq_plan_destroy": (None, [c_void_p]),
+    "ttts_vq_workspace_bytes": (c_size_t, [c_void_p, c_int64]),
+    "ttts_vq_nearest": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_size_t, c_void_p]),
+    "ttts_vq_embed_code": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
+    "ttts_vq_status": (ctypes.c_int, [c_void_p, c_void_p]),
     "ttts_mel_last_error": (c_char_p, []),
     "ttts_mel_version": (c_char_p, []),
 }

@@ -1461,3 +1461,4 @@ extern "C" void ttts_mel_set_experiment(int32_t flags) { g_exp_flags = flags; }
 // ingestion in front of the path (int16 PCM -> float32, sinc resample): include/ttts_ingest.h
 // ------------------------------------------------------------------------------------------
 #include "k_ingest.cuh"
+#include "k_vq.cuh"
