@@ -124,6 +124,59 @@ def test_mel_pth_sink_writes_the_reference_format(tmp_path):
     assert not [f for f in os.listdir(tmp_path) if f.endswith(".tmp")]
 
 
+def _toy_encoder(dim):
+    """Stands in for the DVAE encoder (a model, outside the path): 4 frames -> 1 row, a fixed projection to dim."""
+    w = torch.linspace(-1.0, 1.0, 5 * 4 * dim).reshape(5 * 4, dim)
+
+    def encode(mel_bct, n_frames):
+        B, C, T = mel_bct.shape
+        x = mel_bct[:, :, :T // 4 * 4].reshape(B, C, T // 4, 4).permute(0, 2, 1, 3).reshape(B, T // 4, C * 4)
+        return (x @ w.to(x.device)).contiguous(), n_frames // 4
+    return encode
+
+
+def test_melvq_pth_sink_writes_the_reference_format(tmp_path):
+    """extract_vq.py:26-29: torch.save(code.tolist(), path + '.melvq.pth') with code [1, T'] int64."""
+    from oracle import vq_oracle as vo
+    from xtts_b200.sweep import melvq_pth_sink
+    paths = [str(tmp_path / f"clip{i}.wav") for i in range(3)]
+    embed = vo.synth_codebook(16, 64, 3)
+    mel = torch.randn(2, 5, 12, generator=torch.Generator().manual_seed(1))
+    search = lambda logits: vo.callsite_quantize(logits.numpy(), embed)[2]       # CPU stand-in for the kernel
+    sink = melvq_pth_sink(paths, _toy_encoder(16), None, search=search)
+    sink([2, 0], mel, torch.tensor([12, 9]))
+    a, b = torch.load(paths[2] + ".melvq.pth"), torch.load(paths[0] + ".melvq.pth")
+    assert isinstance(a, list) and len(a) == 1 and len(a[0]) == 3 and all(isinstance(c, int) for c in a[0])
+    assert len(b) == 1 and len(b[0]) == 2
+    logits, _ = _toy_encoder(16)(mel, torch.tensor([12, 9]))
+    assert a == vo.callsite_quantize(logits[0:1].numpy(), embed)[2].tolist()
+    import os
+    assert not [f for f in os.listdir(tmp_path) if f.endswith(".tmp")]
+
+
+@pytest.mark.gpu
+def test_melvq_pth_sink_on_the_gpu_matches_the_cpu_call_sequence(tmp_path):
+    from oracle import vq_oracle as vo
+    from xtts_b200.sweep import melvq_pth_sink
+    from xtts_b200.vq import Quantize
+    paths = [str(tmp_path / f"clip{i}.wav") for i in range(2)]
+    embed = vo.synth_codebook(64, 512, 3)
+    q = Quantize(64, 512)
+    q.embed.copy_(torch.from_numpy(embed))
+    q = q.eval().cuda()
+    mel = torch.randn(2, 5, 400, generator=torch.Generator().manual_seed(1))
+    enc = _toy_encoder(64)
+
+    def enc_same_bits(m, n):                   # the projection on the CPU, so that both sides search identical rows
+        logits, t = enc(m.cpu(), n.cpu())
+        return logits.cuda(), t
+    melvq_pth_sink(paths, enc_same_bits, q)([0, 1], mel.cuda(), torch.tensor([400, 123]).cuda())
+    logits, _ = enc(mel, torch.tensor([400, 123]))
+    want = vo.callsite_quantize(logits.numpy(), embed)[2]
+    assert torch.load(paths[0] + ".melvq.pth") == want[0:1].tolist()
+    assert torch.load(paths[1] + ".melvq.pth") == want[1:2, :30].tolist()
+
+
 @pytest.mark.gpu
 def test_pcm16_corpus_sweep_matches_clip_by_clip_reference(tmp_path):
     """WAV files -> pcm16_fetch -> MelSweep -> .mel.pth files, against load_audio + the V2 call per clip."""

@@ -3,12 +3,15 @@
 Only the hot path: ``TorchMelSpectrogram`` / ``MelSpectrogramFeatures`` / ``dvae_wav_to_mel`` /
 ``make_pad_mask`` (host mirror of the reference interface, ``mel.py``) on top of
 ``libttts_mel.so`` (``csrc/ttts_mel.cu`` behind the C ABI of ``include/ttts_mel.h``), and the ingestion step in
-front of it (``ingest.py``: int16 PCM -> float32 channel 0 -> sinc resample -> clip, ``include/ttts_ingest.h``).
+front of it (``ingest.py``: int16 PCM -> float32 channel 0 -> sinc resample -> clip, ``include/ttts_ingest.h``)
+and the DVAE codebook search behind it (``vq.py``: ``Quantize`` in eval mode, ``include/ttts_vq.h``).
 """
 from .ingest import Resampler, decode_pcm16, get_prompt_slice, load_audio_pcm16, sinc_resample_taps
+from .vq import Quantize, VQPlan, get_codebook_indices
 from .mel import (DEFAULT_MEL_NORM_FILE, MelPlan, MelSpectrogramFeatures, MelSpectrogramFeatures1,
                   TorchMelSpectrogram, dvae_wav_to_mel, make_pad_mask, mel_spectrogram)
 
 __all__ = ["DEFAULT_MEL_NORM_FILE", "MelPlan", "MelSpectrogramFeatures", "MelSpectrogramFeatures1",
            "TorchMelSpectrogram", "dvae_wav_to_mel", "make_pad_mask", "mel_spectrogram",
-           "Resampler", "decode_pcm16", "get_prompt_slice", "load_audio_pcm16", "sinc_resample_taps"]
+           "Resampler", "decode_pcm16", "get_prompt_slice", "load_audio_pcm16", "sinc_resample_taps",
+           "Quantize", "VQPlan", "get_codebook_indices"]

@@ -162,6 +162,34 @@ def mel_pth_done(paths: Sequence[str], suffix: str = ".mel.pth") -> Callable[[in
     return lambda i: os.path.exists(paths[i] + suffix)
 
 
+def melvq_pth_sink(paths: Sequence[str], encode: Callable, codebook, suffix: str = ".melvq.pth",
+                   search: Optional[Callable] = None) -> Callable:
+    """``sink`` that writes what ``process_vq`` writes (ttts/prepare/extract_vq.py:24-29): one file
+    ``<wav path>.melvq.pth`` per clip holding ``torch.save(code.tolist())`` -- a nested Python list ``[[c_0, ...]]``
+    of that clip's codes (``code`` is ``[1, T']``).
+
+    ``encode(mel_bct, n_frames) -> (logits [B, T'max, dim] float32 CUDA, n_tokens [B])`` is the caller's DVAE encoder
+    (``self.encoder(self.norm(mel)).permute(0, 2, 1)``, xtts_dvae.py:327-328: a model, not part of this path);
+    ``codebook`` is an ``xtts_b200.vq.Quantize``.  One codebook search (``k_vq_tc``) and one device->host copy of
+    the indices per batch."""
+    import os
+    if search is None:
+        from .vq import get_codebook_indices
+        search = lambda logits: get_codebook_indices(codebook, logits)       # noqa: E731
+
+    def sink(indices, mel_bct: torch.Tensor, n_frames: torch.Tensor) -> None:
+        logits, n_tokens = encode(mel_bct, n_frames)
+        codes = search(logits).to("cpu")
+        counts = [int(c) for c in (n_tokens.tolist() if torch.is_tensor(n_tokens) else n_tokens)]
+        for b, i in enumerate(indices):
+            out = paths[i] + suffix
+            tmp = out + ".tmp"
+            torch.save(codes[b:b + 1, :counts[b]].tolist(), tmp)
+            os.replace(tmp, out)
+
+    return sink
+
+
 def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, *, kernel_dtype=torch.float32,
                 pinned: bool = True) -> Callable:
     """``fetch`` for corpora of 16-bit PCM: ``read_pcm(i) -> int16 array [frames, channels]`` (the file decode, host
