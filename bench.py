@@ -380,7 +380,8 @@ def run_ours(args):
             vplan.status()
             v_ms = statistics.median(ms_v)
             v_flop = 2.0 * rows * 512 * 8192
-            dist_ref = zs[3].pow(2).sum(1, keepdim=True) - 2 * zs[3] @ emb + emb.pow(2).sum(0, keepdim=True)
+            zl = zs[(3 + 20 - 1) & 3]                      # the batch of the last timed call
+            dist_ref = zl.pow(2).sum(1, keepdim=True) - 2 * zl @ emb + emb.pow(2).sum(0, keepdim=True)
             vq_line = {"workload": "64x216 rows of dim 512 -> nearest of 8192 codes (Quantize.forward, xtts_dvae.py:87-90), resident in HBM",
                        "kernels": {"k_vq_tile": 1, "k_vq_tc": 1, "k_vq_finish": 1}, "ms": v_ms,
                        "rows_per_s": rows / (v_ms * 1e-3),
@@ -389,7 +390,7 @@ def run_ours(args):
                        "executed_frac": 3.0 * v_flop / (v_ms * 1e-3) / 1e12 / tf32_peak,
                        "agreement_with_library_sequence_on_gpu": float(((-dist_ref).max(1)[1] == vind).float().mean()),
                        "l2": "inputs rotate over 4 batches (113 MB of rows); the 33 MB of codebook tiles stay in L2"}
-            del zs, emb, dist_ref
+            del zs, zl, emb, dist_ref
         line = {
             "metric": "log-mel audio-seconds/sec", "value": value, "unit": "audio-s/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",

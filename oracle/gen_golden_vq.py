@@ -2,7 +2,7 @@
 
     python oracle/gen_golden_vq.py            # writes tests/golden/vq_quantize.npz
 
-Imports ``Quantize`` (/root/reference/ttts/vqvae/xtts_dvae.py:50-130) from the read-only reference checkout,
+Imports ``Quantize`` (/root/reference/ttts/vqvae/xtts_dvae.py:52-130) from the read-only reference checkout,
 loads seeded codebooks into its ``embed`` buffer and records what its eval-mode ``forward`` and ``embed_code``
 return.  Inputs are regenerated from the seeds by ``oracle.vq_oracle`` (numpy's legacy generator: version-stable),
 so the full-size case (dim 512, 8192 codes: 16 MB of codebook) costs only its indices in the repository.

@@ -4,16 +4,19 @@ Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s / ``tools/``' CP
 product package (``xtts_b200``) never does.
 
 Parity status: PINNED by ``oracle/gen_golden_vq.py``, which imports the reference's own ``Quantize``
-(/root/reference/ttts/vqvae/xtts_dvae.py:50-130) in the build container, runs its eval-mode forward and
+(/root/reference/ttts/vqvae/xtts_dvae.py:52-130) in the build container, runs its eval-mode forward and
 ``embed_code`` on the seeded inputs below and commits the outputs under ``tests/golden/vq_*.npz``.
 
 Two layers, like ``mel_oracle``:
 
-* ``callsite_quantize`` -- the reference's call sequence (xtts_dvae.py:87-93,117-118) with torch fp32 on the CPU.
+* ``callsite_quantize`` -- the reference's call sequence (xtts_dvae.py:87-93,119-120) with torch fp32 on the CPU.
 * ``restated_distances`` -- |z - e_j|^2 in numpy fp64: the "truth" leg.  The fp32 distances of the reference are
   quantised to ulp(|z|^2 + |e|^2), so near-ties flip with the summation order of the sgemm behind ``@``; an index is
-  therefore accepted when its exact distance is within ``tolerance()`` of the exact minimum, and must EQUAL the exact
-  arg-min wherever the runner-up is further away than that (``check_indices``).  The reference's own indices are
+  therefore accepted when its exact distance is within ``tolerance()`` of the exact minimum, and must BE the exact
+  arg-min (or an exact copy of that code) wherever the runner-up is further away than that (``check_indices``);
+  ``differs_from_exact_argmin`` counts rows that do not return the LOWEST index of the exact minimum -- 0 for the CUDA
+  path (bit-identical scores for identical codes), while the reference's own sgemm rounds two copies of a code
+  differently now and then (MKL, 48 x 200: the higher copy for 4 rows in 300).  The reference's own indices are
   held to the same rule in tests/test_vq.py, so the rule is no looser than the reference's own rounding.
 """
 from __future__ import annotations
@@ -26,7 +29,7 @@ DVAE_DIM, DVAE_N_EMBED = 512, 8192          # ttts/vqvae/config.json:19,22
 
 
 def synth_codebook(dim: int, n_embed: int, seed: int, duplicates: int = 0) -> np.ndarray:
-    """[dim, n_embed] float32 like the module's ``torch.randn(dim, n_embed)`` buffer (xtts_dvae.py:65); numpy's
+    """[dim, n_embed] float32 like the module's ``torch.randn(dim, n_embed)`` buffer (xtts_dvae.py:67); numpy's
     legacy generator, so the bits do not depend on the torch version.  ``duplicates`` copies that many codes to
     higher indices (exact ties: the lowest index must win)."""
     rs = np.random.RandomState(seed)
@@ -62,7 +65,7 @@ def synth_tokens(rows: int, embed: np.ndarray, seed: int, kind: str = "near") ->
 
 
 def callsite_quantize(z, embed):
-    """xtts_dvae.py:87-93,117-118 verbatim in torch fp32 on the CPU.  Returns (quantize, diff, embed_ind)."""
+    """xtts_dvae.py:87-93,119-120 verbatim in torch fp32 on the CPU.  Returns (quantize, diff, embed_ind)."""
     import torch
     import torch.nn.functional as F
     input = torch.as_tensor(z)
@@ -109,18 +112,20 @@ def check_indices(ind: np.ndarray, z: np.ndarray, embed: np.ndarray, ulps: float
         if ((ib < 0) | (ib >= n_embed)).any():
             bad += int(((ib < 0) | (ib >= n_embed)).sum())
             ib = np.clip(ib, 0, n_embed - 1)
-        best = d.argmin(1)                                   # first minimum: the lowest index of an exact tie
+        # the lowest index among the exact minima: duplicated codes tie exactly, but the fp64 table itself carries
+        # ~1e-13 relative rounding that differs between columns, hence the 1e-4-of-tol band
+        dmin0 = d.min(1)
+        best = (d <= (dmin0 + 1e-4 * tol)[:, None]).argmax(1)
         dmin = d[np.arange(len(zb)), best]
         mine = d[np.arange(len(zb)), ib]
-        d2 = d.copy()
-        d2[np.arange(len(zb)), best] = np.inf
-        gap = d2.min(1) - dmin                               # distance of the runner-up
+        d2 = np.where(d <= (dmin0 + 1e-4 * tol)[:, None], np.inf, d)
+        gap = d2.min(1) - dmin                               # distance of the runner-up (exact copies of the winner aside)
         excess = mine - dmin
         worst = max(worst, float((excess / np.maximum(tol, 1e-300)).max()))
         bad += int((excess > tol).sum())
         clear = gap > tol
         decided += int(clear.sum())
-        bad += int((clear & (ib != best)).sum())
+        bad += int((clear & (mine > dmin0 + 1e-4 * tol)).sum())       # a clear winner (or an exact copy of it) is mandatory
         flipped += int((ib != best).sum())
     return {"rows": int(zf.shape[0]), "bad": bad, "differs_from_exact_argmin": flipped, "clear_rows": decided,
             "worst_excess_in_tol": worst}

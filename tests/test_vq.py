@@ -159,9 +159,12 @@ def test_gpu_indices_against_oracle_small_codebooks(kind, rows):
         # both index sets obey the rule, so they can only differ on rows whose runner-up lies within the slack
         # (codebook-independent rows at dim 512: a fraction of a percent); a wrong kernel would be far below
         agree = float((ref == ind.cpu()).float().mean())
-        assert agree >= (0.995 if kind in ("near", "exact") else 0.98), (dim, n_embed, agree)
+        assert agree >= (0.995 if kind == "near" else 0.98), (dim, n_embed, agree)
         if kind == "exact":
-            assert torch.equal(ref, ind.cpu())            # exact ties: the lowest index, like the reference
+            # a row that equals a duplicated code is an exact tie: the lowest index wins (torch.max returns the first
+            # maximum; the reference's own sgemm rounds the two copies differently now and then -- MKL at 48 x 200 returns
+            # the higher copy for 1 row in 300 -- so the exact minimum decides, not the CPU call)
+            assert st["differs_from_exact_argmin"] == 0, (dim, n_embed, st, ref.tolist()[:20], ind.cpu().tolist()[:20])
 
 
 @pytest.mark.gpu

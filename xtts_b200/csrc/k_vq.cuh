@@ -1,7 +1,7 @@
 // k_vq.cuh -- the DVAE codebook search behind the log-mel path (C ABI in include/ttts_vq.h).
 //
-// Reference: Quantize.forward in eval mode, ttts/vqvae/xtts_dvae.py:87-93,117-118,129-130 (called by
-// DiscreteVAE.get_codebook_indices :324-331 from ttts/prepare/extract_vq.py:24-29):
+// Reference: Quantize.forward in eval mode, ttts/vqvae/xtts_dvae.py:87-93,119-120,129-130 (called by
+// DiscreteVAE.get_codebook_indices :327-334 from ttts/prepare/extract_vq.py:24-29):
 //     dist = |z|^2 - 2 z @ embed + |e|^2 ;  embed_ind = argmax(-dist) ;  quantize = embed[:, embed_ind]
 // |z|^2 is the same for every code of a row, so the search is  argmin_j  |e_j|^2 - 2 z . e_j : a
 // [rows x dim] x [dim x n_embed] product with an arg-min epilogue (config.json: dim 512, n_embed 8192:
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(256) k_vq_finish(const unsigned long long* __r
     for (int k = lane; k < dim; k += 32) {
       const float zv = __ldg(zr + k);
       const float d = __fsub_rn(__ldg(e + k), zv);
-      if (quant) quant[row * dim + k] = __fadd_rn(zv, d);    // input + (quantize - input), xtts_dvae.py:118
+      if (quant) quant[row * dim + k] = __fadd_rn(zv, d);    // input + (quantize - input), xtts_dvae.py:120
       acc = fmaf(d, d, acc);
     }
 #pragma unroll

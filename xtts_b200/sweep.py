@@ -169,7 +169,7 @@ def melvq_pth_sink(paths: Sequence[str], encode: Callable, codebook, suffix: str
     of that clip's codes (``code`` is ``[1, T']``).
 
     ``encode(mel_bct, n_frames) -> (logits [B, T'max, dim] float32 CUDA, n_tokens [B])`` is the caller's DVAE encoder
-    (``self.encoder(self.norm(mel)).permute(0, 2, 1)``, xtts_dvae.py:327-328: a model, not part of this path);
+    (``self.encoder(self.norm(mel)).permute(0, 2, 1)``, xtts_dvae.py:330-331: a model, not part of this path);
     ``codebook`` is an ``xtts_b200.vq.Quantize``.  One codebook search (``k_vq_tc``) and one device->host copy of
     the indices per batch."""
     import os

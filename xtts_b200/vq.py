@@ -2,14 +2,14 @@
 
 Reference (file:line in /root/reference):
 
-* ``Quantize``                       ttts/vqvae/xtts_dvae.py:50-130   (forward in eval mode :70-127, embed_code :129-130)
-* ``DiscreteVAE.get_codebook_indices`` xtts_dvae.py:324-331           ``sampled, codes, _ = self.codebook(logits)``
+* ``Quantize``                       ttts/vqvae/xtts_dvae.py:52-130   (forward in eval mode :72-127, embed_code :129-130)
+* ``DiscreteVAE.get_codebook_indices`` xtts_dvae.py:327-334           ``sampled, codes, _ = self.codebook(logits)``
 * caller                             ttts/prepare/extract_vq.py:24-29 (mel -> codes -> ``.melvq.pth``)
 
 Same class name, constructor arguments, buffers (``embed [dim, n_embed]``, ``cluster_size``, ``embed_avg``) and return
 orders as the reference.  What runs on the GPU is the search ``argmax(-dist)`` (tcgen05 kernel ``k_vq_tc``), the
 ``embed_code`` gather, ``diff`` and the straight-through value, behind ``include/ttts_vq.h``.  The EMA codebook update
-of training mode (:104-115) and the balancing heuristic (:71-85) belong to the trainer, not to this path: they raise.
+of training mode (:104-117) and the balancing heuristic (:73-85) belong to the trainer, not to this path: they raise.
 CUDA tensors only -- there is no CPU path here.
 """
 from __future__ import annotations
@@ -135,9 +135,9 @@ class Quantize(nn.Module):
     def forward(self, input, return_soft_codes=False):
         if self.training:
             raise NotImplementedError("Quantize: only eval mode (the get_codebook_indices path) is built; the EMA "
-                                      "codebook update of training (xtts_dvae.py:104-115) belongs to the trainer")
+                                      "codebook update of training (xtts_dvae.py:104-117) belongs to the trainer")
         if self.balancing_heuristic:
-            raise NotImplementedError("Quantize: balancing_heuristic (xtts_dvae.py:71-85, 95-102) is trainer state")
+            raise NotImplementedError("Quantize: balancing_heuristic (xtts_dvae.py:73-85, 95-102) is trainer state")
         if return_soft_codes:
             raise NotImplementedError("Quantize: return_soft_codes materialises the [rows, n_embed] distances, "
                                       "which this path never writes to HBM")
@@ -158,8 +158,8 @@ class Quantize(nn.Module):
 
 @torch.no_grad()
 def get_codebook_indices(codebook: Quantize, logits: torch.Tensor) -> torch.Tensor:
-    """The tail of ``DiscreteVAE.get_codebook_indices`` (xtts_dvae.py:329-331) for encoder output ``logits``
-    ``[B, T', dim]`` (already permuted, :328): the codes alone, without the gather and ``diff``."""
+    """The tail of ``DiscreteVAE.get_codebook_indices`` (xtts_dvae.py:332-334) for encoder output ``logits``
+    ``[B, T', dim]`` (already permuted, :331): the codes alone, without the gather and ``diff``."""
     if logits.device.type != "cuda":
         raise RuntimeError("the codebook search needs a CUDA device (sm_100a); there is no CPU fallback")
     return codebook.plan(logits.device).nearest(logits)[0]
