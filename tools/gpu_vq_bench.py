@@ -67,6 +67,14 @@ def main():
     assert st["bad"] == 0, st
 
     t = timed(lambda i: plan.nearest(zs[i % 4]), a.iters)
+    # clocks under this load: a 1.2 s loop of the same call, sampled by nvidia-smi (bench.py's sampler)
+    from bench import ClockSampler
+    cs = ClockSampler(0)
+    cs.start()
+    for i in range(2500):
+        plan.nearest(zs[i % 4])
+    torch.cuda.synchronize()
+    res["clocks"] = cs.stop()
     t["tflops_algorithmic"] = flop / (t["median_ms"] * 1e-3) / 1e12
     t["rows_per_s"] = a.rows / (t["median_ms"] * 1e-3)
     res["nearest_indices_only"] = t
@@ -87,7 +95,7 @@ def main():
         legs = {}
         for name, flags in (("full", 0), ("no_epilogue", 4), ("no_converters", 1), ("no_codebook_loads", 2),
                             ("mma_only", 1 | 2 | 4), ("converters_only", 2 | 4 | 32), ("codebook_loads_only", 1 | 4 | 32),
-                            ("no_mma", 32)):
+                            ("no_mma", 32), ("full_again", 0)):
             os.environ["TTTS_VQ_EXP"] = str(flags)
             legs[name] = timed(lambda i: plan.nearest(zs[i % 4]), 8)["median_ms"]
         os.environ.pop("TTTS_VQ_EXP")

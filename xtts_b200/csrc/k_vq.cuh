@@ -7,8 +7,8 @@
 // [rows x dim] x [dim x n_embed] product with an arg-min epilogue (config.json: dim 512, n_embed 8192:
 // 8.4 MFLOP per row).  The distances never exist in HBM.
 //
-//   k_vq_tile    z [rows, stride] -> zt [tiles][pairs of k-steps][128 rows][16]: what a converter lane of k_vq_tc
-//                reads per iteration is one contiguous 64-byte run, a warp's 32 lanes 2 KB; also resets the keys
+//   k_vq_tile    z [rows, stride] -> zt [tiles][pairs of k-steps][4][128 rows][4]: each of the four 16-byte loads a
+//                converter warp of k_vq_tc issues per iteration covers 512 contiguous bytes; also resets the keys
 //   k_vq_tc      the search on tcgen05, same machinery as k_resample_tc / k_logmel2: kind::tf32 MMAs with the A operand
 //                (128 rows of z, split hi / lo by converter warps) in TMEM, the B operand (a block of <= 160 codes,
 //                pre-tiled and pre-split at plan creation) in shared memory by cp.async.bulk, 3xTF32 products
@@ -29,13 +29,18 @@ namespace vq {
 constexpr int kTileM = 128;
 constexpr int kConvSets = 3, kEpiSets = 2;
 constexpr int kThreadsTc = 32 * (4 + 4 * kConvSets + 4 * kEpiSets);   // 4 misc + 12 converter + 8 epilogue warps
-constexpr int kStages = 3;             // A ring (TMEM, 64 columns per stage) and B ring (shared memory) share depth and "free" barrier
+constexpr int kStages = 3;             // A ring: TMEM, 64 columns (a quad of k-steps) per stage
+#ifndef VQ_B_STAGES
+#define VQ_B_STAGES 5
+#endif
+constexpr int kBStages = VQ_B_STAGES;  // B ring: shared memory, 40 KB per stage at 160 codes (own "free" barriers; measured
+                                       // equal to a 3-deep ring sharing the A ring's barrier: the kernel is tensor-bound)
 constexpr int kMaxNb = 160;            // codes per block; two accumulator buffers = 320 TMEM columns
 constexpr int kColA = 2 * kMaxNb;      // A ring: columns 320..511
 constexpr int kWarpConv = 4, kWarpEpi = 4 + 4 * kConvSets;
 
 struct Params {
-  const float* zt;            // [tiles][pairs][128][16]
+  const float* zt;            // [tiles][pairs][4 quads of columns][128 rows][4]
   int pairs;                  // pairs of k-steps (16 columns of z each), even: a stage is a quad (32 columns)
   int npass, nbp;             // code blocks, codes per block (multiple of 16)
   const float* codeB;         // [npass][quads][4 k-steps][hi | lo][2 k-halves][nbp][4]
@@ -47,7 +52,7 @@ struct Params {
 };
 
 struct __align__(8) Barriers {
-  uint64_t b_full[kStages];
+  uint64_t b_full[kBStages], b_empty[kBStages];
   uint64_t a_full[kStages], a_empty[kStages];
   uint64_t acc_full[2], acc_empty[2];
 };
@@ -82,7 +87,7 @@ __global__ void __launch_bounds__(256) k_vq_tile(const float* __restrict__ z, lo
     }
     const long long tile = row / kTileM;
     const int r = (int)(row - tile * kTileM);
-    *reinterpret_cast<float4*>(zt + (((tile * pairs + (c >> 2)) * kTileM + r) * 16 + 4 * (c & 3))) = v;
+    *reinterpret_cast<float4*>(zt + ((((tile * pairs + (c >> 2)) * 4 + (c & 3)) * kTileM + r) * 4)) = v;
     if (c == 0) keys[row] = ~0ull;
   }
 }
@@ -93,13 +98,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
   const uint32_t b_stage_bytes = (uint32_t)P.nbp * 256u;     // 4 k-steps x 2 arrays x 2 k-halves x nbp rows x 16 B
   const int nquads = P.pairs >> 1;
   uint8_t* s_b = smem_vq;
-  Barriers* bars = reinterpret_cast<Barriers*>(s_b + (size_t)kStages * b_stage_bytes);
+  Barriers* bars = reinterpret_cast<Barriers*>(s_b + (size_t)kBStages * b_stage_bytes);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
+    for (int i = 0; i < kBStages; ++i) { mbar_init(smem_u32(&bars->b_full[i]), 1); mbar_init(smem_u32(&bars->b_empty[i]), 1); }
     for (int i = 0; i < kStages; ++i) {
-      mbar_init(smem_u32(&bars->b_full[i]), 1);
       mbar_init(smem_u32(&bars->a_full[i]), 8);              // 2 pairs x 4 lane quarters per quad
       mbar_init(smem_u32(&bars->a_empty[i]), 1);
     }
@@ -122,8 +127,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
       for (long long u = blockIdx.x; u < P.units; u += gridDim.x) {
         const int pass = (int)(u % P.npass);
         for (int ks = 0; ks < nquads; ++ks, ++seq) {
-          const uint32_t st = seq % kStages, use = seq / kStages;
-          mbar_wait(smem_u32(&bars->a_empty[st]), (use & 1) ^ 1, P.status, 1101);   // one "stage free" barrier for A and B
+          const uint32_t st = seq % kBStages, use = seq / kBStages;
+          mbar_wait(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 1101);
           const uint32_t full = smem_u32(&bars->b_full[st]);
           mbar_expect_tx(full, b_stage_bytes);
           bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
@@ -145,12 +150,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
       const uint32_t d = tmem + abuf * kMaxNb;
       if (!(P.exp & 4)) mbar_wait(smem_u32(&bars->acc_empty[abuf]), (ause_acc & 1) ^ 1, P.status, 1201);
       for (int ks = 0; ks < nquads; ++ks, ++kseq) {
-        const uint32_t st = kseq % kStages, use = kseq / kStages;
-        if (!(P.exp & 1)) mbar_wait(smem_u32(&bars->a_full[st]), use & 1, P.status, 1202);
+        const uint32_t as = kseq % kStages, ause = kseq / kStages;
+        const uint32_t st = kseq % kBStages, use = kseq / kBStages;
+        if (!(P.exp & 1)) mbar_wait(smem_u32(&bars->a_full[as]), ause & 1, P.status, 1202);
         if (!(P.exp & 2)) mbar_wait(smem_u32(&bars->b_full[st]), use & 1, P.status, 1203);
         tc_fence_after();
         if (elect_one_sync()) {
-          const uint32_t a0 = tmem + kColA + st * 64;
+          const uint32_t a0 = tmem + kColA + as * 64;
           const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
           if (!(P.exp & 32)) {
 #pragma unroll
@@ -163,7 +169,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
               mma_tf32_ts(d, a_hi, b_hi, idesc, 1u);
             }
           }
-          tc_commit(smem_u32(&bars->a_empty[st]));         // frees the A stage and the B stage
+          tc_commit(smem_u32(&bars->a_empty[as]));
+          tc_commit(smem_u32(&bars->b_empty[st]));
           if (ks == nquads - 1) tc_commit(smem_u32(&bars->acc_full[abuf]));
         }
         __syncwarp();
@@ -181,9 +188,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
       int pr = kConvSets * it + set;
       if (pr >= P.pairs) pr = P.pairs - 1;                         // phantom: any valid address, never used
       const long long tile = u / P.npass;
-      const float4* src = reinterpret_cast<const float4*>(P.zt + ((tile * P.pairs + pr) * kTileM + q * 32 + lane) * 16);
+      const float4* src = reinterpret_cast<const float4*>(P.zt + (tile * P.pairs + pr) * (kTileM * 16)) + q * 32 + lane;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] = __ldg(src + i);
+      for (int i = 0; i < 4; ++i) v[i] = __ldg(src + i * kTileM);         // 512 contiguous bytes per warp and load
     };
     long long c_u = blockIdx.x;
     int c_it = 0;
@@ -300,7 +307,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
   }
 }
 
-inline size_t smem_bytes(int nbp) { return (size_t)kStages * nbp * 256 + sizeof(Barriers) + 16; }
+inline size_t smem_bytes(int nbp) { return (size_t)kBStages * nbp * 256 + sizeof(Barriers) + 16; }
 
 // ------------------------------------------------------------------------------------------------ k_vq_finish
 // One warp per row.
