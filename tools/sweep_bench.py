@@ -17,6 +17,7 @@ from xtts_b200.sweep import MelSweep, norms_from_stats
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--utts", type=int, default=100000)
+ap.add_argument("--max-clips", type=int, default=256, help="clips per length-sorted batch")
 args = ap.parse_args()
 world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
 torch.cuda.set_device(local)
@@ -27,9 +28,9 @@ plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n
                power=2.0, norm="slaney", device=dev)
 rng = np.random.default_rng(4321)
 lens = [int(round(22050 * u)) for u in rng.uniform(1.0, 30.0, size=args.utts)]
-sweep = MelSweep(plan, lens, max_clips=64, rank=rank, world_size=world)   # length-sorted batches of 64
+sweep = MelSweep(plan, lens, max_clips=args.max_clips, rank=rank, world_size=world)   # length-sorted batches
 mine = sweep.my_buckets()
-pool = torch.rand(64 * 661500 + 4096, device=dev, generator=torch.Generator(device=dev).manual_seed(1234 + rank)) * 2 - 1
+pool = torch.rand(args.max_clips * 661500 + 4096, device=dev, generator=torch.Generator(device=dev).manual_seed(1234 + rank)) * 2 - 1
 len_dev = {b.indices: torch.tensor([lens[i] for i in b.indices], device=dev) for b in mine}
 
 
@@ -65,7 +66,7 @@ if rank == 0:
     frames = int(acc[160].item())
     audio = sum(lens) / 22050
     my_frames = sum(b.frames for b in mine)
-    print(json.dumps({"workload": f"sweep_{args.utts}_utts_1-30s", "n_gpus": world, "ms": float(ms), "wall_s": wall,
+    print(json.dumps({"workload": f"sweep_{args.utts}_utts_1-30s", "n_gpus": world, "max_clips": args.max_clips, "batches_rank0": len(mine), "ms": float(ms), "wall_s": wall,
                       "audio_s_per_s": audio / (float(ms) * 1e-3), "frames_per_s": frames / (float(ms) * 1e-3),
                       "frames_total": frames, "frames_expected": sum(1 + L // 256 for L in lens),
                       "buckets": len(sweep.buckets), "rank0_frames_share": my_frames / frames,
