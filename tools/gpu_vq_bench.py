@@ -95,7 +95,8 @@ def main():
         legs = {}
         for name, flags in (("full", 0), ("no_epilogue", 4), ("no_converters", 1), ("no_codebook_loads", 2),
                             ("mma_only", 1 | 2 | 4), ("converters_only", 2 | 4 | 32), ("codebook_loads_only", 1 | 4 | 32),
-                            ("no_mma", 32), ("full_again", 0)):
+                            ("no_mma", 32), ("one_product", 8), ("one_product_mma_only", 8 | 1 | 2 | 4),
+                            ("full_again", 0)):
             os.environ["TTTS_VQ_EXP"] = str(flags)
             legs[name] = timed(lambda i: plan.nearest(zs[i % 4]), 8)["median_ms"]
         os.environ.pop("TTTS_VQ_EXP")

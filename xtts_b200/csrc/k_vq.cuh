@@ -10,7 +10,7 @@
 //   k_vq_tile    z [rows, stride] -> zt [tiles][pairs of k-steps][4][128 rows][4]: each of the four 16-byte loads a
 //                converter warp of k_vq_tc issues per iteration covers 512 contiguous bytes; also resets the keys
 //   k_vq_tc      the search on tcgen05, same machinery as k_resample_tc / k_logmel2: kind::tf32 MMAs with the A operand
-//                (128 rows of z, split hi / lo by converter warps) in TMEM, the B operand (a block of <= 160 codes,
+//                (128 rows of z, split hi / lo by converter warps) in TMEM, the B operand (a block of <= 192 codes,
 //                pre-tiled and pre-split at plan creation) in shared memory by cp.async.bulk, 3xTF32 products
 //                (lo*hi + hi*lo + hi*hi: fp32-grade dot products), two accumulator buffers; the epilogue warps keep a
 //                running (score, index) per row and merge blocks with one 64-bit atomicMin per row and unit on the
@@ -29,14 +29,16 @@ namespace vq {
 constexpr int kTileM = 128;
 constexpr int kConvSets = 3, kEpiSets = 2;
 constexpr int kThreadsTc = 32 * (4 + 4 * kConvSets + 4 * kEpiSets);   // 4 misc + 12 converter + 8 epilogue warps
-constexpr int kStages = 3;             // A ring: TMEM, 64 columns (a quad of k-steps) per stage
+#ifndef VQ_NB
+#define VQ_NB 192                      // measured on one box: 160 -> 0.508 ms, 176 -> 0.498, 192 -> 0.487 (64 x 216 rows, 8192 codes):
+#endif                                 // fewer, longer MMAs (96 cycles) and 43 instead of 52 conversions of every row tile
+constexpr int kMaxNb = VQ_NB;          // codes per block; two accumulator buffers = 2 x VQ_NB TMEM columns
+constexpr int kStages = (512 - 2 * kMaxNb) / 64;   // A ring: TMEM, 64 columns (a quad of k-steps) per stage
 #ifndef VQ_B_STAGES
-#define VQ_B_STAGES 5
+#define VQ_B_STAGES ((220 * 1024) / (VQ_NB * 256) < 5 ? (220 * 1024) / (VQ_NB * 256) : 5)
 #endif
-constexpr int kBStages = VQ_B_STAGES;  // B ring: shared memory, 40 KB per stage at 160 codes (own "free" barriers; measured
-                                       // equal to a 3-deep ring sharing the A ring's barrier: the kernel is tensor-bound)
-constexpr int kMaxNb = 160;            // codes per block; two accumulator buffers = 320 TMEM columns
-constexpr int kColA = 2 * kMaxNb;      // A ring: columns 320..511
+constexpr int kBStages = VQ_B_STAGES;  // B ring: shared memory, 48 KB per stage at 192 codes, 4 deep (own "free" barriers)
+constexpr int kColA = 2 * kMaxNb;      // A ring: the columns behind the accumulators
 constexpr int kWarpConv = 4, kWarpEpi = 4 + 4 * kConvSets;
 
 struct Params {
@@ -164,6 +166,10 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
               const uint32_t a_hi = a0 + 16 * h, a_lo = a_hi + 8;
               const uint64_t b_hi = ((uint64_t)desc_hi << 32) | (lo + 2 * h * arr16);
               const uint64_t b_lo = ((uint64_t)desc_hi << 32) | (lo + (2 * h + 1) * arr16);
+              if (P.exp & 8) {                                 // timing experiment: one product instead of three
+                mma_tf32_ts(d, a_hi, b_hi, idesc, (ks == 0 && h == 0) ? 0u : 1u);
+                continue;
+              }
               mma_tf32_ts(d, a_lo, b_hi, idesc, (ks == 0 && h == 0) ? 0u : 1u);
               mma_tf32_ts(d, a_hi, b_lo, idesc, 1u);
               mma_tf32_ts(d, a_hi, b_hi, idesc, 1u);
@@ -178,63 +184,62 @@ __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
     }
   } else if (warp >= kWarpConv && warp < kWarpEpi && !(P.exp & 1)) {
     // ===== converters =====
-    // Iteration `it` of set `set` (of 3) covers the pair of k-steps 3 it + set of the unit: lane = row, 16 columns of
-    // z = four 16-byte loads (one contiguous 2 KB run per warp), fetched one iteration ahead across unit boundaries,
-    // split into TF32-exact hi and the remainder lo, 4 x tcgen05.st.x8 into the quad's TMEM stage.
+    // Per pair of k-steps: lane = row, 16 columns of z = four 16-byte loads, fetched one item ahead, split into
+    // TF32-exact hi and the remainder lo, 4 x tcgen05.st.x8 into the quad's TMEM stage.
     const int cw = warp - kWarpConv, set = cw >> 2, q = warp & 3;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    const int iters = (P.pairs + kConvSets - 1) / kConvSets;      // pairs per set, rounded up (phantom pairs skipped)
-    auto fetch = [&](float4 (&v)[4], long long u, int it) {
-      int pr = kConvSets * it + set;
-      if (pr >= P.pairs) pr = P.pairs - 1;                         // phantom: any valid address, never used
-      const long long tile = u / P.npass;
-      const float4* src = reinterpret_cast<const float4*>(P.zt + (tile * P.pairs + pr) * (kTileM * 16)) + q * 32 + lane;
+    // A set walks the CTA's pairs of k-steps as one sequence across units (g = unit * pairs + pair, g = set mod 3): its
+    // consecutive items are never more than two quads apart, so the parity wait on a stage's "free" barrier cannot be
+    // two phases ahead of the barrier (with a per-unit restart the gap at a unit boundary is three quads: a 2-deep A
+    // ring then aliases and deadlocks).
+    const long long my_units = (P.units - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    struct Cur { long long ui; int pr; };
+    auto fetch = [&](float4 (&v)[4], const Cur& c) {
+      const long long tile = (blockIdx.x + c.ui * gridDim.x) / P.npass;
+      const float4* src = reinterpret_cast<const float4*>(P.zt + (tile * P.pairs + c.pr) * (kTileM * 16)) + q * 32 + lane;
 #pragma unroll
       for (int i = 0; i < 4; ++i) v[i] = __ldg(src + i * kTileM);         // 512 contiguous bytes per warp and load
     };
-    long long c_u = blockIdx.x;
-    int c_it = 0;
-    if (c_u < P.units) {
+    auto step = [&](Cur& c) {
+      c.pr += kConvSets;
+      while (c.pr >= P.pairs) { c.pr -= P.pairs; ++c.ui; }
+    };
+    Cur c{0, set};
+    while (c.pr >= P.pairs) { c.pr -= P.pairs; ++c.ui; }
+    if (c.ui < my_units) {
       float4 cur[4], nxt[4];
-      fetch(cur, c_u, c_it);
-      uint32_t qseq = 0;                                     // quads of all earlier units
+      fetch(cur, c);
       for (;;) {
-        long long n_u = c_u;
-        int n_it = c_it + 1;
-        if (n_it >= iters) { n_it = 0; n_u += gridDim.x; }
-        const bool n_valid = n_u < P.units;
-        if (n_valid) fetch(nxt, n_u, n_it);
-        const int pr = kConvSets * c_it + set;
-        if (pr < P.pairs) {
-          uint32_t hi[16], lo[16];
+        Cur n = c;
+        step(n);
+        const bool n_valid = n.ui < my_units;
+        if (n_valid) fetch(nxt, n);
+        uint32_t hi[16], lo[16];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const float rv[4] = {cur[c].x, cur[c].y, cur[c].z, cur[c].w};
+        for (int k = 0; k < 4; ++k) {
+          const float rv[4] = {cur[k].x, cur[k].y, cur[k].z, cur[k].w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t hb = __float_as_uint(rv[j]) & 0xFFFFE000u;
-              hi[4 * c + j] = hb;
-              lo[4 * c + j] = __float_as_uint(rv[j] - __uint_as_float(hb));
-            }
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t hb = __float_as_uint(rv[j]) & 0xFFFFE000u;
+            hi[4 * k + j] = hb;
+            lo[4 * k + j] = __float_as_uint(rv[j] - __uint_as_float(hb));
           }
-          const uint32_t qs = qseq + (uint32_t)(pr >> 1);
-          const uint32_t as = qs % kStages, ause = qs / kStages;
-          const uint32_t a_base = tmem + lane_addr + kColA + as * 64 + (uint32_t)(pr & 1) * 32;
-          mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 1402);
-          tc_fence_after();
-          tmem_st8(a_base, hi);
-          tmem_st8(a_base + 8, lo);
-          tmem_st8(a_base + 16, hi + 8);
-          tmem_st8(a_base + 24, lo + 8);
-          tmem_wait_st();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
         }
-        if (n_u != c_u) qseq += (uint32_t)nquads;            // that was this unit's last iteration
+        const uint32_t qs = (uint32_t)c.ui * (uint32_t)nquads + (uint32_t)(c.pr >> 1);     // quad sequence number
+        const uint32_t as = qs % kStages, ause = qs / kStages;
+        const uint32_t a_base = tmem + lane_addr + kColA + as * 64 + (uint32_t)(c.pr & 1) * 32;
+        mbar_wait(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 1402);
+        tc_fence_after();
+        tmem_st8(a_base, hi);
+        tmem_st8(a_base + 8, lo);
+        tmem_st8(a_base + 16, hi + 8);
+        tmem_st8(a_base + 24, lo + 8);
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->a_full[as]));
         if (!n_valid) break;
-        c_u = n_u;
-        c_it = n_it;
+        c = n;
 #pragma unroll
         for (int j = 0; j < 4; ++j) cur[j] = nxt[j];
       }
