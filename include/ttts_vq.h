@@ -48,6 +48,14 @@ int ttts_vq_nearest(const ttts_vq_plan* plan, const float* z_dev, int64_t row_st
                     int64_t* embed_ind_dev, float* quantize_dev_or_null, float* diff_dev_or_null,
                     void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* The same search for the encoder's own output layout [B, dim, T] (channel-major), i.e. `get_codebook_indices`
+ * without the `permute((0, 2, 1))` + `reshape` copy of xtts_dvae.py:331,87: row n = b T + t.  Indices only.
+ *   z_dev [B, dim, T] float32 with element (b, k, t) at b * batch_stride + k * chan_stride + t
+ *   embed_ind_dev [B * T] int64 (= [B, T]) */
+int ttts_vq_nearest_bct(const ttts_vq_plan* plan, const float* z_dev, int64_t batch_stride, int64_t chan_stride,
+                        int64_t B, int64_t T, int64_t* embed_ind_dev,
+                        void* workspace_dev, size_t workspace_bytes, void* stream);
+
 /* `Quantize.embed_code` (xtts_dvae.py:129-130): out[i, :] = embed[:, embed_ind[i]].  Indices outside
  * [0, n_embed) raise the device status (checked by ttts_vq_status) and produce zeros. */
 int ttts_vq_embed_code(const ttts_vq_plan* plan, const int64_t* embed_ind_dev, int64_t n_rows,

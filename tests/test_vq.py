@@ -101,6 +101,7 @@ def test_c_abi_argument_checks_without_a_gpu(built_lib):
     assert b"n_embed" in built_lib.ttts_mel_last_error()
     assert built_lib.ttts_vq_workspace_bytes(None, 100) == 0
     assert built_lib.ttts_vq_nearest(None, None, 0, 0, None, None, None, None, 0, None) < 0
+    assert built_lib.ttts_vq_nearest_bct(None, None, 0, 0, 0, 0, None, None, 0, None) < 0
     built_lib.ttts_vq_plan_destroy(None)
 
 
@@ -197,6 +198,28 @@ def test_gpu_full_size_batch_properties():
     e_sel = embed.T[ind.cpu().numpy()].astype(np.float64)
     want = float(((e_sel - z.astype(np.float64)) ** 2).mean())
     assert abs(float(diff) - want) <= 1e-5 * want
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,T,dim,n_embed", [(3, 100, 64, 512), (2, 217, 512, 8192), (1, 5, 80, 1000), (5, 1, 48, 200)])
+def test_gpu_encoder_layout_search_equals_row_major(B, T, dim, n_embed):
+    """get_codebook_indices on the permuted view of a [B, dim, T] encoder output (xtts_dvae.py:331) searches it in
+    place (ttts_vq_nearest_bct); same indices as the reshape-copy path, also for a strided batch."""
+    from xtts_b200.vq import get_codebook_indices
+    embed = vo.synth_codebook(dim, n_embed, 5)
+    z = vo.synth_tokens(B * T, embed, 6, "near").reshape(B, T, dim)
+    q = _module(embed)
+    plan = q.plan(torch.device("cuda", 0))
+    want = plan.nearest(torch.from_numpy(z).cuda())[0]
+    enc_out = torch.from_numpy(np.ascontiguousarray(z.transpose(0, 2, 1))).cuda()          # [B, dim, T]
+    got = get_codebook_indices(q, enc_out.permute(0, 2, 1))
+    plan.status()
+    assert got.shape == (B, T) and got.dtype == torch.int64 and torch.equal(got, want)
+    wide = torch.zeros(B, dim + 3, T + 5, device="cuda")
+    wide[:, :dim, :T] = enc_out
+    assert torch.equal(plan.nearest_bct(wide[:, :dim, :T]), want)                            # batch / channel strides
+    st = vo.check_indices(got.cpu().numpy(), z, embed)
+    assert st["bad"] == 0, st
 
 
 @pytest.mark.gpu

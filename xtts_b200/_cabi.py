@@ -63,6 +63,8 @@ SYMBOLS = {
     "ttts_vq_workspace_bytes": (c_size_t, [c_void_p, c_int64]),
     "ttts_vq_nearest": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                        c_void_p, c_size_t, c_void_p]),
+    "ttts_vq_nearest_bct": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p,
+                                           c_void_p, c_size_t, c_void_p]),
     "ttts_vq_embed_code": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
     "ttts_vq_status": (ctypes.c_int, [c_void_p, c_void_p]),
     "ttts_mel_last_error": (c_char_p, []),

@@ -94,6 +94,33 @@ __global__ void __launch_bounds__(256) k_vq_tile(const float* __restrict__ z, lo
   }
 }
 
+// Channel-major input z[b, k, t] (the DVAE encoder's own output layout, before the permute of xtts_dvae.py:331): row
+// n = b T + t.  One thread = one row x four consecutive channels; consecutive threads take consecutive rows, so both
+// the four loads (along t) and the 16-byte store (along the tile's rows) are coalesced.
+__global__ void __launch_bounds__(256) k_vq_tile_cm(const float* __restrict__ z, long long batch_stride,
+                                                    long long chan_stride, long long T, long long n_rows, int dim,
+                                                    int pairs, long long rows_pad, float* __restrict__ zt,
+                                                    unsigned long long* __restrict__ keys) {
+  const int cpr = pairs * 4;
+  const long long total = rows_pad * cpr;
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += 256LL * gridDim.x) {
+    const int c = (int)(i / rows_pad), k = 4 * c;
+    const long long row = i - (long long)c * rows_pad;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (row < n_rows) {
+      const long long b = row / T, t = row - b * T;
+      const float* src = z + b * batch_stride + (long long)k * chan_stride + t;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (k + j < dim) v[j] = __ldg(src + j * chan_stride);
+    }
+    const long long tile = row / kTileM;
+    const int r = (int)(row - tile * kTileM);
+    *reinterpret_cast<float4*>(zt + ((((tile * pairs + (c >> 2)) * 4 + (c & 3)) * kTileM + r) * 4)) = make_float4(v[0], v[1], v[2], v[3]);
+    if (c == 0) keys[row] = ~0ull;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ k_vq_tc
 __global__ void __launch_bounds__(kThreadsTc, 1) k_vq_tc(const Params P) {
   extern __shared__ __align__(1024) uint8_t smem_vq[];
@@ -475,11 +502,11 @@ extern "C" size_t ttts_vq_workspace_bytes(const ttts_vq_plan* p, int64_t n_rows)
   return vq_layout(p, n_rows).total;
 }
 
-extern "C" int ttts_vq_nearest(const ttts_vq_plan* p, const float* z, int64_t row_stride, int64_t n_rows,
-                               int64_t* ind, float* quant, float* diff, void* ws, size_t ws_bytes, void* stream) {
-  if (!p || !z || !ind || !ws) return fail(TTTS_MEL_EINVAL, "null argument");
-  if (n_rows <= 0) return fail(TTTS_MEL_EINVAL, "empty input (n_rows=%lld)", (long long)n_rows);
-  if (row_stride < p->dim) return fail(TTTS_MEL_EINVAL, "row_stride %lld < dim %d", (long long)row_stride, p->dim);
+namespace {
+// z_rm != null: rows [n_rows, row_stride]; else channel-major z_cm[b, k, t] with n_rows = B T
+int vq_nearest_impl(const ttts_vq_plan* p, const float* z_rm, int64_t row_stride, const float* z_cm, int64_t batch_stride,
+                    int64_t chan_stride, int64_t T, int64_t n_rows, int64_t* ind, float* quant, float* diff, void* ws,
+                    size_t ws_bytes, void* stream) {
   int cur_dev = -1;
   CUDA_TRY(cudaGetDevice(&cur_dev));
   if (cur_dev != p->device) return fail(TTTS_MEL_EINVAL, "plan lives on device %d, the current device is %d", p->device, cur_dev);
@@ -492,11 +519,15 @@ extern "C" int ttts_vq_nearest(const ttts_vq_plan* p, const float* z, int64_t ro
   auto* keys = (unsigned long long*)(w + l.keys);
   float* row_err = (float*)(w + l.row_err);
   const long long rows_pad = l.tiles * vq::kTileM;
-  const int vec_ok = (row_stride % 4 == 0) && ((uintptr_t)z % 16 == 0);
   {
     const long long total = rows_pad * p->pairs * 4;
     const int grid = (int)std::min<long long>((total + 255) / 256, (long long)p->num_sms * 16);
-    vq::k_vq_tile<<<grid, 256, 0, st>>>(z, row_stride, n_rows, p->dim, p->pairs, rows_pad, zt, keys, vec_ok);
+    if (z_rm) {
+      const int vec_ok = (row_stride % 4 == 0) && ((uintptr_t)z_rm % 16 == 0);
+      vq::k_vq_tile<<<grid, 256, 0, st>>>(z_rm, row_stride, n_rows, p->dim, p->pairs, rows_pad, zt, keys, vec_ok);
+    } else {
+      vq::k_vq_tile_cm<<<grid, 256, 0, st>>>(z_cm, batch_stride, chan_stride, T, n_rows, p->dim, p->pairs, rows_pad, zt, keys);
+    }
   }
   vq::Params q;
   q.zt = zt; q.pairs = p->pairs; q.npass = p->npass; q.nbp = p->nbp; q.codeB = p->d_codeB; q.ee = p->d_ee;
@@ -508,7 +539,7 @@ extern "C" int ttts_vq_nearest(const ttts_vq_plan* p, const float* z, int64_t ro
   }
   {
     const int grid = (int)std::min<long long>((n_rows + 7) / 8, (long long)p->num_sms * 16);
-    vq::k_vq_finish<<<grid, 256, 0, st>>>(keys, n_rows, z, row_stride, p->dim, p->d_embT, (long long*)ind, quant,
+    vq::k_vq_finish<<<grid, 256, 0, st>>>(keys, n_rows, z_rm, row_stride, p->dim, p->d_embT, (long long*)ind, quant,
                                           diff ? row_err : nullptr);
   }
   int launches = 3;
@@ -519,6 +550,24 @@ extern "C" int ttts_vq_nearest(const ttts_vq_plan* p, const float* z, int64_t ro
   CUDA_TRY(cudaGetLastError());
   g_launches = launches;
   return 0;
+}
+}  // namespace
+
+extern "C" int ttts_vq_nearest(const ttts_vq_plan* p, const float* z, int64_t row_stride, int64_t n_rows,
+                               int64_t* ind, float* quant, float* diff, void* ws, size_t ws_bytes, void* stream) {
+  if (!p || !z || !ind || !ws) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (n_rows <= 0) return fail(TTTS_MEL_EINVAL, "empty input (n_rows=%lld)", (long long)n_rows);
+  if (row_stride < p->dim) return fail(TTTS_MEL_EINVAL, "row_stride %lld < dim %d", (long long)row_stride, p->dim);
+  return vq_nearest_impl(p, z, row_stride, nullptr, 0, 0, 0, n_rows, ind, quant, diff, ws, ws_bytes, stream);
+}
+
+extern "C" int ttts_vq_nearest_bct(const ttts_vq_plan* p, const float* z, int64_t batch_stride, int64_t chan_stride,
+                                   int64_t B, int64_t T, int64_t* ind, void* ws, size_t ws_bytes, void* stream) {
+  if (!p || !z || !ind || !ws) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || T <= 0) return fail(TTTS_MEL_EINVAL, "empty input (B=%lld T=%lld)", (long long)B, (long long)T);
+  if (chan_stride < T || batch_stride < chan_stride * p->dim)
+    return fail(TTTS_MEL_EINVAL, "strides (%lld, %lld) too small for [B, %d, %lld]", (long long)batch_stride, (long long)chan_stride, p->dim, (long long)T);
+  return vq_nearest_impl(p, nullptr, 0, z, batch_stride, chan_stride, T, B * T, ind, nullptr, nullptr, ws, ws_bytes, stream);
 }
 
 extern "C" int ttts_vq_embed_code(const ttts_vq_plan* p, const int64_t* ind, int64_t n_rows, float* out,

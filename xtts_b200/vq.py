@@ -84,6 +84,31 @@ class VQPlan:
         shape = tuple(z.shape[:-1])
         return ind.view(shape), (quant.view(*shape, self.dim) if quant is not None else None), diff
 
+    def nearest_bct(self, z: torch.Tensor) -> torch.Tensor:
+        """z ``[B, dim, T]`` float32 CUDA (the encoder's own layout; any batch / channel strides, unit stride along T)
+        -> embed_ind int64 ``[B, T]``: the search without the permute + reshape copy."""
+        if z.device != self.device:
+            raise RuntimeError(f"input on {z.device}, plan on {self.device}")
+        if z.dtype != torch.float32:
+            raise TypeError(f"expected float32 input, got {z.dtype}")
+        if z.dim() != 3 or z.shape[1] != self.dim:
+            raise RuntimeError(f"expected [B, {self.dim}, T], got {tuple(z.shape)}")
+        B, _, T = (int(v) for v in z.shape)
+        if B == 0 or T == 0:
+            raise RuntimeError("empty input")
+        if z.stride(2) != 1 or z.stride(1) < T or z.stride(0) < z.stride(1) * self.dim:
+            z = z.contiguous()
+        lib = _cabi.lib()
+        with torch.cuda.device(self.device):
+            ind = torch.empty((B, T), dtype=torch.int64, device=self.device)
+            ws_bytes = int(lib.ttts_vq_workspace_bytes(self._h, B * T))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            _cabi.check(lib.ttts_vq_nearest_bct(self._h, z.data_ptr(), int(z.stride(0)), int(z.stride(1)), B, T,
+                                                ind.data_ptr(), ws.data_ptr(), ws_bytes, stream))
+            ws.record_stream(torch.cuda.current_stream(self.device))
+        return ind
+
     def embed_code(self, embed_id: torch.Tensor) -> torch.Tensor:
         if embed_id.device != self.device:
             raise RuntimeError(f"indices on {embed_id.device}, plan on {self.device}")
@@ -162,4 +187,9 @@ def get_codebook_indices(codebook: Quantize, logits: torch.Tensor) -> torch.Tens
     ``[B, T', dim]`` (already permuted, :331): the codes alone, without the gather and ``diff``."""
     if logits.device.type != "cuda":
         raise RuntimeError("the codebook search needs a CUDA device (sm_100a); there is no CPU fallback")
-    return codebook.plan(logits.device).nearest(logits)[0]
+    plan = codebook.plan(logits.device)
+    if logits.dim() == 3 and logits.dtype == torch.float32 and logits.stride(1) == 1 and logits.stride(2) >= logits.shape[1] \
+            and logits.shape[0] > 0 and logits.shape[1] > 1:
+        # a permuted view of the encoder's [B, dim, T'] output (xtts_dvae.py:331): search it where it lies
+        return plan.nearest_bct(logits.permute(0, 2, 1))
+    return plan.nearest(logits)[0]
