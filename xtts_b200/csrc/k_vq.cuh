@@ -70,10 +70,10 @@ __device__ __forceinline__ unsigned long long make_key(float score, uint32_t idx
 __global__ void __launch_bounds__(256) k_vq_tile(const float* __restrict__ z, long long row_stride, long long n_rows,
                                                  int dim, int pairs, long long rows_pad, float* __restrict__ zt,
                                                  unsigned long long* __restrict__ keys, int vec_ok) {
-  const int cpr = pairs * 4;                                // float4 chunks per row
+  const unsigned cpr = (unsigned)pairs * 4u;                // float4 chunks per row
   const long long total = rows_pad * cpr;
   for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += 256LL * gridDim.x) {
-    const long long row = i / cpr;
+    const long long row = total <= 0xFFFFFFFFLL ? (long long)((unsigned)i / cpr) : i / cpr;
     const int c = (int)(i - row * cpr), k = 4 * c;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (row < n_rows) {
@@ -98,25 +98,21 @@ __global__ void __launch_bounds__(256) k_vq_tile(const float* __restrict__ z, lo
 // n = b T + t.  One thread = one row x four consecutive channels; consecutive threads take consecutive rows, so both
 // the four loads (along t) and the 16-byte store (along the tile's rows) are coalesced.
 __global__ void __launch_bounds__(256) k_vq_tile_cm(const float* __restrict__ z, long long batch_stride,
-                                                    long long chan_stride, long long T, long long n_rows, int dim,
-                                                    int pairs, long long rows_pad, float* __restrict__ zt,
+                                                    long long chan_stride, unsigned T, unsigned n_rows, int dim,
+                                                    int pairs, unsigned rows_pad, float* __restrict__ zt,
                                                     unsigned long long* __restrict__ keys) {
-  const int cpr = pairs * 4;
-  const long long total = rows_pad * cpr;
-  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += 256LL * gridDim.x) {
-    const int c = (int)(i / rows_pad), k = 4 * c;
-    const long long row = i - (long long)c * rows_pad;
+  const int c = blockIdx.y, k = 4 * c;                      // grid.y = float4 chunks per row: no 64-bit divisions
+  for (unsigned row = blockIdx.x * 256u + threadIdx.x; row < rows_pad; row += 256u * gridDim.x) {
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     if (row < n_rows) {
-      const long long b = row / T, t = row - b * T;
+      const unsigned b = row / T, t = row - b * T;
       const float* src = z + b * batch_stride + (long long)k * chan_stride + t;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         if (k + j < dim) v[j] = __ldg(src + j * chan_stride);
     }
-    const long long tile = row / kTileM;
-    const int r = (int)(row - tile * kTileM);
-    *reinterpret_cast<float4*>(zt + ((((tile * pairs + (c >> 2)) * 4 + (c & 3)) * kTileM + r) * 4)) = make_float4(v[0], v[1], v[2], v[3]);
+    const unsigned tile = row / kTileM, r = row % kTileM;
+    *reinterpret_cast<float4*>(zt + ((((long long)tile * pairs + (c >> 2)) * 4 + (c & 3)) * kTileM + r) * 4) = make_float4(v[0], v[1], v[2], v[3]);
     if (c == 0) keys[row] = ~0ull;
   }
 }
@@ -510,6 +506,7 @@ int vq_nearest_impl(const ttts_vq_plan* p, const float* z_rm, int64_t row_stride
   int cur_dev = -1;
   CUDA_TRY(cudaGetDevice(&cur_dev));
   if (cur_dev != p->device) return fail(TTTS_MEL_EINVAL, "plan lives on device %d, the current device is %d", p->device, cur_dev);
+  if (n_rows > 0x7FFFFF00LL) return fail(TTTS_MEL_EINVAL, "n_rows %lld: split the batch (limit 2^31 - 256)", (long long)n_rows);
   const VqLayout l = vq_layout(p, n_rows);
   if (ws_bytes < l.total) return fail(TTTS_MEL_EINVAL, "workspace %zu < %zu bytes", ws_bytes, l.total);
   if ((uintptr_t)ws % 256) return fail(TTTS_MEL_EINVAL, "workspace not 256-byte aligned");
@@ -526,7 +523,9 @@ int vq_nearest_impl(const ttts_vq_plan* p, const float* z_rm, int64_t row_stride
       const int vec_ok = (row_stride % 4 == 0) && ((uintptr_t)z_rm % 16 == 0);
       vq::k_vq_tile<<<grid, 256, 0, st>>>(z_rm, row_stride, n_rows, p->dim, p->pairs, rows_pad, zt, keys, vec_ok);
     } else {
-      vq::k_vq_tile_cm<<<grid, 256, 0, st>>>(z_cm, batch_stride, chan_stride, T, n_rows, p->dim, p->pairs, rows_pad, zt, keys);
+      const unsigned gx = (unsigned)std::min<long long>((rows_pad + 255) / 256, (long long)p->num_sms * 4);
+      vq::k_vq_tile_cm<<<dim3(gx, (unsigned)(p->pairs * 4)), 256, 0, st>>>(z_cm, batch_stride, chan_stride, (unsigned)T, (unsigned)n_rows,
+                                                                         p->dim, p->pairs, (unsigned)rows_pad, zt, keys);
     }
   }
   vq::Params q;
