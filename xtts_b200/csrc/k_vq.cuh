@@ -9,6 +9,7 @@
 //
 //   k_vq_tile    z [rows, stride] -> zt [tiles][pairs of k-steps][4][128 rows][4]: each of the four 16-byte loads a
 //                converter warp of k_vq_tc issues per iteration covers 512 contiguous bytes; also resets the keys
+//   k_vq_tile_cm the same from the encoder's channel-major output [B, dim, T'] (ttts_vq_nearest_bct)
 //   k_vq_tc      the search on tcgen05, same machinery as k_resample_tc / k_logmel2: kind::tf32 MMAs with the A operand
 //                (128 rows of z, split hi / lo by converter warps) in TMEM, the B operand (a block of <= 192 codes,
 //                pre-tiled and pre-split at plan creation) in shared memory by cp.async.bulk, 3xTF32 products
@@ -34,6 +35,9 @@ constexpr int kThreadsTc = 32 * (4 + 4 * kConvSets + 4 * kEpiSets);   // 4 misc 
 #endif                                 // fewer, longer MMAs (96 cycles) and 43 instead of 52 conversions of every row tile
 constexpr int kMaxNb = VQ_NB;          // codes per block; two accumulator buffers = 2 x VQ_NB TMEM columns
 constexpr int kStages = (512 - 2 * kMaxNb) / 64;   // A ring: TMEM, 64 columns (a quad of k-steps) per stage
+// a converter set's consecutive items are up to two quads apart; a parity wait must never be two phases ahead of its
+// barrier, i.e. that distance must not exceed the ring depth (see the converter loop)
+static_assert(kStages >= 2 && kMaxNb % 16 == 0 && kMaxNb <= 256, "VQ_NB: multiple of 16, at most 192 for a 2-deep A ring");
 #ifndef VQ_B_STAGES
 #define VQ_B_STAGES ((220 * 1024) / (VQ_NB * 256) < 5 ? (220 * 1024) / (VQ_NB * 256) : 5)
 #endif
@@ -49,7 +53,8 @@ struct Params {
   const float* ee;            // [npass * nbp] |e_j|^2, +inf for the padding codes of the last block
   unsigned long long* keys;   // [tiles * 128]
   long long units;            // tiles * npass
-  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no codebook loads, 4 no epilogue, 32 no MMAs
+  int exp;                    // timing experiments (RESULTS INVALID): 1 no converters, 2 no codebook loads, 4 no epilogue,
+                              // 8 one product per k-step instead of three, 32 no MMAs
   int32_t* status;
 };
 
