@@ -37,15 +37,15 @@ for name, B, L, it in (("C1 1x10s", 1, 220500, 200), ("C2 64x10s", 64, 220500, 1
 # C3: 256 ragged clips through the bucketed sweep (masks + n_frames + stats)
 rng = np.random.default_rng(1234)
 lens = [int(round(22050 * u)) for u in rng.uniform(1.0, 30.0, size=256)]
-for bsec in (2.0, 30.0):
-    sweep = MelSweep(plan, lens, bucket_seconds=bsec, max_clips=64)
+for bsec, mc in ((2.0, 64), (30.0, 64), (30.0, 256)):
+    sweep = MelSweep(plan, lens, bucket_seconds=bsec, max_clips=mc)
     batches = {}
     for b in sweep.buckets:
         wav = torch.rand(len(b.indices), b.max_len, device=dev, generator=g) * 2 - 1
         batches[b.indices] = (wav, torch.tensor([lens[i] for i in b.indices], device=dev))
     fetch = lambda idx, max_len: batches[tuple(idx)]
     ms = timed(lambda: sweep.run_stats(fetch), 10)
-    out[f"C3 256 ragged 1-30s, {bsec:g} s buckets (masks+stats)"] = dict(ms=ms, audio_s_per_s=sum(lens) / 22050 / (ms * 1e-3),
+    out[f"C3 256 ragged 1-30s, {bsec:g} s buckets of <= {mc} (masks+stats)"] = dict(ms=ms, audio_s_per_s=sum(lens) / 22050 / (ms * 1e-3),
         frames_per_s=sum(1 + L // 256 for L in lens) / (ms * 1e-3), buckets=len(sweep.buckets),
         padded_over_real=sum(b.max_len * len(b.indices) for b in sweep.buckets) / sum(lens))
     del batches

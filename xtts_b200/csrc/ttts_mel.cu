@@ -677,7 +677,10 @@ __global__ void __launch_bounds__(256) k_pad(const float* __restrict__ wav, int6
   const float* __restrict__ src = wav + (int64_t)b * row_stride;
   float* __restrict__ dst = xp + (int64_t)b * Lp;
   const bool okL = (L > pad) && (L <= Lmax);
-  for (int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i4 < Lp;
+  // only what this clip's frames read: its own L + 2 pad samples (a ragged batch of 1..30 s clips is 2/3 padding;
+  // writing zeros over all of it made this kernel 0.29 ms for 256 clips, 40 % of the log-mel kernel's time)
+  const int64_t Lb = okL ? min(Lp, (L + 2 * (int64_t)pad + 3) & ~(int64_t)3) : 0;
+  for (int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i4 < Lb;
        i4 += (int64_t)gridDim.x * blockDim.x * 4) {
     float4 v;
     const int64_t s0 = i4 - pad;
@@ -1288,7 +1291,9 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   ++g_launches;
   if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
-    dim3 grid((unsigned)((vecs + 255) / 256 > 4096 ? 4096 : (vecs + 255) / 256), (unsigned)B);
+    // grid-stride over each clip's own extent: with ragged lengths most blocks of a (Lp / 1024)-wide grid had nothing to do
+    const int64_t per_clip = std::min<int64_t>((vecs + 255) / 256, B >= 64 ? 48 : (B >= 8 ? 256 : 4096));
+    dim3 grid((unsigned)per_clip, (unsigned)B);
     k_pad<<<grid, 256, 0, stream>>>(wav, row_stride, lengths, Lmax, p->cfg.pad, w.xp, w.Lp, vec_ok);
     ++g_launches;
   }

@@ -100,10 +100,13 @@ def decode_pcm16(pcm: torch.Tensor, frames: Optional[torch.Tensor] = None) -> to
     device = pcm.device
     lib = _cabi.lib()
     with torch.cuda.device(device):
-        out = torch.empty((B, F), dtype=torch.float32, device=device)
+        # rows on a 16-byte pitch (a view of [B, pitch]): the log-mel kernel then reads the batch in place instead of
+        # copying it into its padded workspace first
+        pitch = (F + 3) // 4 * 4
+        out = torch.empty((B, pitch), dtype=torch.float32, device=device)[:, :F]
         stream = torch.cuda.current_stream(device).cuda_stream
         _cabi.check(lib.ttts_pcm16_to_f32(pcm.data_ptr(), F * C, C, fr.data_ptr() if fr is not None else None,
-                                          B, F, out.data_ptr(), F, stream))
+                                          B, F, out.data_ptr(), pitch, stream))
     return out
 
 
