@@ -13,7 +13,8 @@ lens = sorted(int(round(22050 * u)) for u in rng.uniform(1.0, 30.0, size=256))
 if len(sys.argv) > 1 and sys.argv[1] == "unsorted":
     rng.shuffle(lens)
 L = torch.tensor(lens, device=dev)
-x = torch.rand(256, max(lens), device=dev) * 2 - 1
+width = max(lens) if "aligned" not in sys.argv else (max(lens) + 3) // 4 * 4      # "aligned": rows on a 16-byte pitch -> read in place
+x = (torch.rand(256, width, device=dev) * 2 - 1)[:, :max(lens)]
 for _ in range(3):
     y = plan.forward(x, lengths=L)
 torch.cuda.synchronize()
@@ -22,4 +23,4 @@ for _ in range(10):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); y = plan.forward(x, lengths=L); e1.record(); torch.cuda.synchronize()
     ts.append(e0.elapsed_time(e1))
-print("forward ms", sorted(ts)[5], "audio-s", sum(lens) / 22050, "frames", sum(1 + l // 256 for l in lens))
+print("pitch", x.stride(0), "forward ms", sorted(ts)[5], "audio-s", sum(lens) / 22050, "frames", sum(1 + l // 256 for l in lens))
