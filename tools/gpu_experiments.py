@@ -6,9 +6,16 @@ import torch
 from xtts_b200 import MelPlan, _cabi
 dev = torch.device("cuda:0")
 lib = _cabi.lib()
-plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
-               power=2.0, norm="slaney", device=dev)
-x = torch.rand(64, 220500, device=dev) * 2 - 1
+V2 = "--v2" in sys.argv          # the MelSpectrogramFeatures parametrisation (24 kHz, 100 mel, 512 live bins, power 1)
+if V2:
+    sys.argv.remove("--v2")
+    plan = MelPlan(sample_rate=24000, n_fft=1024, hop_length=256, win_length=1024, n_mels=100, f_min=0, f_max=None,
+                   power=1.0, norm=None, clamp=1e-7, device=dev)
+    x = torch.rand(64, 240000, device=dev) * 2 - 1
+else:
+    plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
+                   power=2.0, norm="slaney", device=dev)
+    x = torch.rand(64, 220500, device=dev) * 2 - 1
 names = {0: "full", 1: "no A handoff", 2: "no basis loads", 4: "no epilogue", 3: "MMA+epilogue only", 5: "no A, no epi",
          6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only", 32: "no MMAs", 36: "no MMAs, no epilogue", 38: "converters only (no MMA/basis/epi)", 34: "no MMAs, no basis",
          35: "epilogue only", 43: "epilogue only, no drain math", 51: "epilogue only, no log pass", 59: "epilogue only: TMEM loads + barriers",

@@ -32,7 +32,10 @@ constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 fol
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
 constexpr int kSlotFloats = 20;                  // 12 forward taps + 8 mirrored taps; 80 B pitch: conflict-free LDS.128
 constexpr int kStageBytes = kSlots * kSlotFloats * 4;
-constexpr int kDepth = 2;                        // raw-audio stages per converter warp
+#ifndef F2_DEPTH
+#define F2_DEPTH 2
+#endif
+constexpr int kDepth = F2_DEPTH;                 // raw-audio stages per converter warp
 constexpr int kPieces = kSlots * 5;              // 16 B pieces per stage
 constexpr int kPieceIters = (kPieces + 31) / 32;
 constexpr int kConvWarps2 = 4 * kSets;
@@ -53,7 +56,10 @@ constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
 constexpr int kRegsMisc = F2_REGS_MISC, kRegsConv = F2_REGS_CONV, kRegsEpi = F2_REGS_EPI;
 static_assert(128 * kRegsMisc + 384 * kRegsConv + 512 * kRegsEpi <= 65536, "register budgets exceed the file");
 constexpr int kBStages2 = 4;                      // basis ring depth (single CTA: 4 x 24 KB)
-constexpr int kBStagesPair = 8;                   // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
+#ifndef F2_BSTAGES_PAIR
+#define F2_BSTAGES_PAIR 8
+#endif
+constexpr int kBStagesPair = F2_BSTAGES_PAIR;     // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
 constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
 constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
 #ifndef F2_QR_UNROLL
@@ -175,7 +181,7 @@ __device__ __forceinline__ uint32_t mbar_try_wait_cluster(uint32_t bar, uint32_t
 // bounded wait with cluster-scope acquire (barriers the peer CTA arrives on)
 __device__ __noinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int32_t* status, int code) {
   const long long t0 = clock64();
-  while (!mbar_try_wait_cluster(bar, parity)) {
+  while (!mbar_try_wait_hint(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
   }
 }

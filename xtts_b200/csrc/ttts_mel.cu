@@ -501,10 +501,29 @@ __device__ __forceinline__ void mbar_timeout(int32_t* status, int code) {
   __threadfence_system();
   __trap();
 }
+// Slow path: try_wait with a suspend-time hint, so that a waiting warp sleeps in hardware (it wakes as soon as the phase
+// completes) instead of re-issuing the probe every ~80 cycles -- ncu of round 1 showed 58 % of all issued warp
+// instructions in these loops, competing with the converter warps for issue slots.
+#ifndef TTTS_WAIT_HINT_NS
+#define TTTS_WAIT_HINT_NS 20000
+#endif
+__device__ __forceinline__ uint32_t mbar_try_wait_hint(uint32_t bar, uint32_t parity) {
+#if TTTS_WAIT_HINT_NS > 0
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity), "r"((uint32_t)TTTS_WAIT_HINT_NS) : "memory");
+  return ok;
+#else
+  return mbar_try_wait(bar, parity);
+#endif
+}
 template <int kRole>
 __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, int32_t* status, int code) {
   const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
+  while (!mbar_try_wait_hint(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
   }
 }
