@@ -14,7 +14,9 @@
  * Nothing in ttts_mel_forward allocates or synchronises.
  *
  * Threading: a plan is immutable after create/set_norms; forward is re-entrant across
- * streams as long as each in-flight call has its own workspace.
+ * streams and threads as long as each in-flight call has its own workspace.  The library keeps no
+ * process-global state that can change a result and never reads the environment (kernel-selection
+ * and leg-removal knobs exist only in the lab build, include/ttts_mel_lab.h).
  *
  * Errors: every int function returns 0 on success or a negative TTTS_MEL_E* code;
  * ttts_mel_last_error() returns a thread-local message for the last failure.
@@ -74,6 +76,12 @@ void ttts_mel_plan_destroy(ttts_mel_plan* plan);
  * 1 + (length + 2*pad - n_fft) / hop, or TTTS_MEL_EINVAL when length <= pad (reflect needs it). */
 int64_t ttts_mel_frames(const ttts_mel_plan* plan, int64_t length);
 
+/* Plan queries: the bin range the plan computes (rows of the filterbank with a non-zero weight: bins outside it are
+ * never evaluated). */
+int32_t ttts_mel_first_bin(const ttts_mel_plan* plan);
+int32_t ttts_mel_num_bins(const ttts_mel_plan* plan);   /* padded bin count                                 */
+int32_t ttts_mel_live_bins(const ttts_mel_plan* plan);  /* bins with a non-zero filterbank row span          */
+
 /* Bytes of device workspace ttts_mel_forward needs for a batch of B clips of at most Lmax samples. */
 size_t ttts_mel_workspace_bytes(const ttts_mel_plan* plan, int32_t B, int64_t Lmax);
 
@@ -95,25 +103,18 @@ int ttts_mel_forward(const ttts_mel_plan* plan, const float* wav_dev, int64_t ro
                      float* mel_out_dev, int32_t* n_frames_dev_or_null, uint8_t* mask_dev_or_null,
                      void* workspace_dev, size_t workspace_bytes, void* stream);
 
-/* Same contract, computed by a plain CUDA-core fp32 kernel (no tensor cores, no pipeline).
- * A second, independent device implementation used by the GPU tests to cross-check the tcgen05
- * kernel at sizes the CPU oracle cannot reach.  Not a fallback: nothing dispatches to it. */
-int ttts_mel_forward_simt(const ttts_mel_plan* plan, const float* wav_dev, int64_t row_stride,
-                          const int64_t* lengths_dev_or_null, int32_t B, int64_t Lmax, int32_t Tmax,
-                          float* mel_out_dev, int32_t* n_frames_dev_or_null, uint8_t* mask_dev_or_null,
-                          void* workspace_dev, size_t workspace_bytes, void* stream);
-
-/* ttts_mel_forward plus a dump of the DFT stage for stage-level parity tests:
- *   reim_out_dev [total_frames, 2*n_bins] fp32: per frame (clips concatenated, valid frames only)
- *   n_bins real parts then n_bins imaginary-part magnitudes, bins ttts_mel_first_bin(plan) .. +n_bins. */
-int ttts_mel_forward_debug(const ttts_mel_plan* plan, const float* wav_dev, int64_t row_stride,
+/* ttts_mel_forward with stage (4) fused into the kernel's log pass: the per-channel sufficient statistics of the
+ * UN-normalised log-mel of this batch's valid frames are added to acc_dev[2*n_mels+1] fp64 = [sum_m | sumsq_m | frames]
+ * (same meaning as ttts_mel_stats_accumulate, without the extra pass over HBM).  Inside the launch the sums are kept
+ * in 64-bit fixed point (steps of 2^-32 and 2^-24), so they are bit-identical from run to run and independent of
+ * how a corpus is cut into batches or sharded over GPUs up to the final fp64 additions.  acc_dev is NOT zeroed. */
+int ttts_mel_forward_stats(const ttts_mel_plan* plan, const float* wav_dev, int64_t row_stride,
                            const int64_t* lengths_dev_or_null, int32_t B, int64_t Lmax, int32_t Tmax,
                            float* mel_out_dev, int32_t* n_frames_dev_or_null, uint8_t* mask_dev_or_null,
-                           void* workspace_dev, size_t workspace_bytes, void* stream,
-                           float* reim_out_dev);
-int32_t ttts_mel_first_bin(const ttts_mel_plan* plan);
-int32_t ttts_mel_num_bins(const ttts_mel_plan* plan);   /* padded bin count (columns of the dump / 2) */
-int32_t ttts_mel_live_bins(const ttts_mel_plan* plan);  /* bins with a non-zero filterbank row span   */
+                           void* workspace_dev, size_t workspace_bytes, void* stream, double* acc_dev);
+
+/* sizeof(ttts_mel_config) as the library was built: a binding asserts its own struct against it. */
+size_t ttts_mel_config_size(void);
 
 /* Synchronises `stream` and returns the device-side status word of the workspace's last call:
  * 0, or TTTS_MEL_EDEVICE with the reason in ttts_mel_last_error(). */
@@ -131,18 +132,6 @@ int ttts_mel_stats_accumulate(const ttts_mel_plan* plan, const float* logmel_dev
 
 /* Kernel launches the last ttts_mel_forward* call on this thread enqueued (for bench accounting). */
 int32_t ttts_mel_last_launch_count(void);
-
-/* Measurement hooks: when enabled, every ttts_mel_forward records a library-owned CUDA event pair
- * around the fused log-mel kernel on the launch stream (up to max_calls calls; 0 disables).
- * ttts_mel_profile_collect synchronises the device, writes the per-call kernel durations in ms and
- * returns how many were written (then restarts the ring). */
-int ttts_mel_profile_enable(int32_t max_calls);
-int ttts_mel_profile_collect(float* ms_out, int32_t capacity);
-
-/* Timing experiments for kernel development (RESULTS ARE INVALID while a flag is set; tools/gpu_experiments.py):
- * 1 removes the converter -> MMA operand handoff, 2 the basis loads, 4 the epilogue, 8 the drain arithmetic (the
- * accumulators are still read), 16 the log pass, 32 the MMAs themselves.  0 restores normal operation. */
-void ttts_mel_set_experiment(int32_t flags);
 
 const char* ttts_mel_last_error(void);
 const char* ttts_mel_version(void);

@@ -339,4 +339,21 @@ def synth(kind: str, B: int, L: int, seed: int) -> np.ndarray:
         f = 440.0 * (1.0 + np.arange(B, dtype=np.float64)[:, None])
         x = 0.5 * np.sin(2 * np.pi * f * t / 22050.0) + 1e-3 * rng.standard_normal((B, L))
         return x.astype(np.float32)
+    # clean high-dynamic-range inputs (SURVEY.md 8c ii: "pure tone", "1/f"), no added noise floor
+    if kind == "puretone":
+        t = np.arange(L, dtype=np.float64)[None, :]
+        f = 440.0 * (1.0 + np.arange(B, dtype=np.float64)[:, None])
+        return (0.5 * np.sin(2 * np.pi * f * t / 22050.0)).astype(np.float32)
+    if kind == "tone_silence":      # half a second of tone, digital silence, tone again (speech-like on/off structure)
+        x = synth("puretone", B, L, seed)
+        seg = max(1, L // 3)
+        x[:, seg:2 * seg] = 0.0
+        return x
+    if kind == "pink":              # 1/f noise: white spectrum shaped by f^-1/2 in amplitude, peak-normalised to 0.5
+        w = rng.standard_normal((B, L))
+        X = np.fft.rfft(w, axis=-1)
+        f = np.arange(X.shape[-1], dtype=np.float64)
+        f[0] = 1.0
+        y = np.fft.irfft(X / np.sqrt(f)[None, :], n=L, axis=-1)
+        return (0.5 * y / np.abs(y).max(axis=-1, keepdims=True)).astype(np.float32)
     raise ValueError(kind)

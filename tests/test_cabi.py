@@ -14,10 +14,18 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _header_symbols():
     names = set()
     for h in ("ttts_mel.h", "ttts_ingest.h", "ttts_vq.h"):
-        src = open(os.path.join(ROOT, "include", h)).read()
-        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-        names |= set(re.findall(r"\b(ttts_[a-z0-9_]+)\s*\(", src))
+        names |= _symbols_of(h)
+    names |= _symbols_of("ttts_mel_lab.h", lab=False)        # the measurement hooks both libraries export
     return sorted(names)
+
+
+def _symbols_of(header, lab=None):
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    if lab is not None:                                      # split ttts_mel_lab.h at its #ifdef TTTS_MEL_LAB block
+        m = re.search(r"#ifdef TTTS_MEL_LAB\n(.*?)#endif", src, flags=re.S)
+        src = m.group(1) if lab else src.replace(m.group(0), "")
+    return set(re.findall(r"\b(ttts_[a-z0-9_]+)\s*\(", src))
 
 
 def test_library_exports_every_declared_symbol(built_lib):
@@ -27,6 +35,35 @@ def test_library_exports_every_declared_symbol(built_lib):
         assert getattr(built_lib, n) is not None, n
     from xtts_b200 import _cabi
     assert sorted(_cabi.SYMBOLS) == names       # the ctypes table and the header agree
+
+
+def test_lab_library_adds_only_the_lab_header(built_lib):
+    """libttts_mel_lab.so = the product symbols + include/ttts_mel_lab.h's lab block; the product library exports none of
+    the lab block (no leg-removal switch, no environment knob can change what it computes)."""
+    from xtts_b200 import _cabi
+    lab_only = sorted(_symbols_of("ttts_mel_lab.h", lab=True))
+    assert lab_only == sorted(_cabi.LAB_SYMBOLS) and "ttts_mel_set_experiment" in lab_only
+    lab = _cabi.lab()
+    for n in lab_only:
+        assert getattr(lab, n) is not None
+        assert not hasattr(built_lib, n), n
+    strings = subprocess.run(["strings", _cabi.LIB_PATH], capture_output=True, text=True).stdout
+    assert "TTTS_MEL_ALGO" not in strings and "TTTS_VQ_EXP" not in strings and "TTTS_RESAMPLE_EXP" not in strings
+
+
+def test_integration_stub_matches_the_header(built_lib):
+    """the ctypes block a maintainer would paste is executed against the built library
+    (round 1 shipped a 7-field struct there while the header had 8)."""
+    from xtts_b200 import _cabi
+    md = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    block = next(b for b in re.findall(r"```python\n(.*?)```", md, flags=re.S) if "class _Cfg(Structure)" in b)
+    ns = {}
+    exec(block.replace('ctypes.CDLL("libttts_mel.so")', f'ctypes.CDLL({_cabi.LIB_PATH!r})'), ns)
+    assert ctypes.sizeof(ns["_Cfg"]) == built_lib.ttts_mel_config_size() == ctypes.sizeof(_cabi.MelConfig) == 32
+    assert [f[0] for f in ns["_Cfg"]._fields_] == [f[0] for f in _cabi.MelConfig._fields_]
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "ttts_mel.h")).read(), flags=re.S)
+    body = re.search(r"typedef struct ttts_mel_config \{(.*?)\} ttts_mel_config;", hdr, flags=re.S).group(1)
+    assert re.findall(r"\b(\w+);", body) == [f[0] for f in _cabi.MelConfig._fields_]
 
 
 def test_library_is_sm100a_with_tcgen05_and_tma(built_lib):

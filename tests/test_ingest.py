@@ -242,14 +242,18 @@ def test_gpu_fused_decode_resample_is_bit_identical_to_two_steps(rates, channels
 @gpu
 def test_gpu_decimator_agrees_with_general_kernel(monkeypatch):
     """k_decimate (2:1 / 3:1 / 4:1 fast path) against k_resample on the same plan inputs."""
-    from xtts_b200 import Resampler
+    from xtts_b200 import Resampler, _cabi
     x = torch.rand((5, 50021), device="cuda") * 2 - 1
     lens = torch.tensor([50021, 1, 2, 33333, 4099])
     for o, n in ((44100, 22050), (48000, 16000), (32000, 8000)):
-        fast = Resampler(o, n)
+        fast = Resampler(o, n)                                # product library: its default kernel choice
+        _cabi.select_lab(True)                                # kernel-selection knobs exist in the lab build only
         monkeypatch.setenv("TTTS_RESAMPLE_GENERIC", "1")
-        slow = Resampler(o, n)
-        monkeypatch.delenv("TTTS_RESAMPLE_GENERIC")
+        try:
+            slow = Resampler(o, n)
+        finally:
+            monkeypatch.delenv("TTTS_RESAMPLE_GENERIC")
+            _cabi.select_lab(False)
         ya, la = fast(x, lens)
         yb, lb = slow(x, lens)
         assert torch.equal(la, lb)
@@ -260,14 +264,18 @@ def test_gpu_decimator_agrees_with_general_kernel(monkeypatch):
 @pytest.mark.parametrize("rates", [(44100, 24000), (16000, 22050), (24000, 22050), (44100, 16000), (48000, 22050)])
 def test_gpu_tensor_core_resampler_agrees_with_fma_kernel(monkeypatch, rates):
     """k_resample_tc (tcgen05, 3xTF32) against k_resample (fp32 FMA) on the same plan inputs, ragged."""
-    from xtts_b200 import Resampler
+    from xtts_b200 import Resampler, _cabi
     o, n = rates
     x = torch.rand((6, 40013), device="cuda") * 2 - 1
     lens = torch.tensor([40013, 1, 2, 33333, 4099, 20000])
-    fast = Resampler(o, n)
+    fast = Resampler(o, n)                                    # product library: its default kernel choice
+    _cabi.select_lab(True)                                    # kernel-selection knobs exist in the lab build only
     monkeypatch.setenv("TTTS_RESAMPLE_SIMT", "1")
-    slow = Resampler(o, n)
-    monkeypatch.delenv("TTTS_RESAMPLE_SIMT")
+    try:
+        slow = Resampler(o, n)
+    finally:
+        monkeypatch.delenv("TTTS_RESAMPLE_SIMT")
+        _cabi.select_lab(False)
     ya, la = fast(x, lens, clip=True)
     yb, lb = slow(x, lens, clip=True)
     assert torch.equal(la, lb)

@@ -204,10 +204,18 @@ def test_pcm16_corpus_sweep_matches_clip_by_clip_reference(tmp_path):
         ref = orc.callsite_logmel(wav, orc.V2, None)
         assert got.shape == ref.shape and got.dtype == torch.float32
         assert float((got - ref).abs().max()) <= 2e-3     # log of |.| amplifies the 3e-7 resample tolerance near the clamp
-    # resume: everything exists now, nothing is fetched again
+    # resume: everything exists now.  The statistics still cover the whole corpus (a resumed sweep must derive
+    # the same mel_norms), nothing is written again, and the file pass does not even fetch
+    stamps = [os.stat(p + ".mel.pth").st_mtime_ns for p in paths]
+    acc2 = sweep.run_stats(fetch, done=mel_pth_done(paths), sink=mel_pth_sink(paths))
+    assert torch.equal(acc2, acc)                                   # fixed-point statistics: bit-identical run to run
+    assert stamps == [os.stat(p + ".mel.pth").st_mtime_ns for p in paths]
     calls = []
-    sweep.run_stats(lambda idx, m: calls.append(idx), done=mel_pth_done(paths))
+    assert sweep.run_files(lambda idx, m: calls.append(idx), mel_pth_sink(paths), done=mel_pth_done(paths)) == 0
     assert calls == []
+    # the module that owns the plan still applies ITS norms (none here) after the sweep touched the plan
+    x = torch.rand(1, 24000, device="cuda:0") * 2 - 1
+    assert float((mod(x) - orc.callsite_logmel(x.cpu(), orc.V2, None).to("cuda:0")).abs().max()) <= 1e-4
 
 
 def test_numa_binding_reads_sysfs_and_degrades_quietly(tmp_path, monkeypatch):

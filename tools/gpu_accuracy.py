@@ -9,7 +9,7 @@ from xtts_b200 import MelPlan
 
 dev = torch.device("cuda:0")
 plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
-               power=2.0, norm="slaney", device=dev)
+               power=2.0, norm="slaney", device=dev, lab=True)
 res = []
 for seed in range(int(sys.argv[1]) if len(sys.argv) > 1 else 4):
     for kind in ("uniform", "gauss"):

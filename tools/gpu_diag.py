@@ -10,7 +10,7 @@ dev = torch.device("cuda:0")
 print(torch.cuda.get_device_name(0), flush=True)
 norms = orc.default_mel_norms(80)
 plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
-               power=2.0, norm="slaney", device=dev)
+               power=2.0, norm="slaney", device=dev, lab=True)
 print("plan: first_bin", plan.first_bin, "num_bins", plan.num_bins, "live", plan.live_bins, flush=True)
 
 def run(B, L, impl, seed=1):
@@ -52,7 +52,7 @@ print("DFT re err (rel to max)", np.abs(re - st.re[:, k0:k0 + live]).max() / sca
       " im err", np.abs(im - (-st.im[:, k0:k0 + live])).max() / scale, flush=True)
 
 # timing of the headline config
-x = torch.rand(64, 220500, device=dev) * 2 - 1
+x = torch.rand(64, 220500, device=dev, lab=True) * 2 - 1
 for impl in ("tcgen05", "simt"):
     for _ in range(3):
         plan.forward(x, impl=impl)

@@ -5,16 +5,16 @@ sys.path.insert(0, ROOT)
 import torch
 from xtts_b200 import MelPlan, _cabi
 dev = torch.device("cuda:0")
-lib = _cabi.lib()
+lib = _cabi.lab()          # leg removal exists in the lab build only (include/ttts_mel_lab.h)
 V2 = "--v2" in sys.argv          # the MelSpectrogramFeatures parametrisation (24 kHz, 100 mel, 512 live bins, power 1)
 if V2:
     sys.argv.remove("--v2")
     plan = MelPlan(sample_rate=24000, n_fft=1024, hop_length=256, win_length=1024, n_mels=100, f_min=0, f_max=None,
-                   power=1.0, norm=None, clamp=1e-7, device=dev)
+                   power=1.0, norm=None, clamp=1e-7, device=dev, lab=True)
     x = torch.rand(64, 240000, device=dev) * 2 - 1
 else:
     plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
-                   power=2.0, norm="slaney", device=dev)
+                   power=2.0, norm="slaney", device=dev, lab=True)
     x = torch.rand(64, 220500, device=dev) * 2 - 1
 names = {0: "full", 1: "no A handoff", 2: "no basis loads", 4: "no epilogue", 3: "MMA+epilogue only", 5: "no A, no epi",
          6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only", 32: "no MMAs", 36: "no MMAs, no epilogue", 38: "converters only (no MMA/basis/epi)", 34: "no MMAs, no basis",
@@ -26,12 +26,11 @@ for flags in FLAGS:
     for _ in range(3):
         plan.forward(x)
     torch.cuda.synchronize()
-    lib.ttts_mel_profile_enable(20)
+    plan.profile_enable(20)
     for _ in range(20):
         plan.forward(x)
-    buf = (ctypes.c_float * 20)()
-    n = lib.ttts_mel_profile_collect(buf, 20)
-    ms = sorted(buf[i] for i in range(n))
+    ms = sorted(plan.profile_collect(20))
+    n = len(ms)
     print(f"flags={flags} ({names.get(flags, "?"):>20s}): k_logmel median {ms[n//2]*1e3:7.1f} us  min {ms[0]*1e3:7.1f} us", flush=True)
-    lib.ttts_mel_profile_enable(0)
+    plan.profile_enable(0)
 lib.ttts_mel_set_experiment(0)

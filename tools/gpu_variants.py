@@ -39,13 +39,12 @@ def worker(so):
         else:
             torch.save(y0.cpu(), ref_path)
         n = 200
-        lib.ttts_mel_profile_enable(n)
+        plan.profile_enable(n)
         for i in range(n):
             plan.forward(xs[i & 3])
-        buf = (ctypes.c_float * n)()
-        k = lib.ttts_mel_profile_collect(buf, n)
-        lib.ttts_mel_profile_enable(0)
-        ms = sorted(buf[i] for i in range(k))
+        ms = sorted(plan.profile_collect(n))
+        k = len(ms)
+        plan.profile_enable(0)
         res[name + "_us_median"] = round(ms[k // 2] * 1e3, 2)
         res[name + "_us_min"] = round(ms[0] * 1e3, 2)
         plan.status()

@@ -419,7 +419,7 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
   p->rows = (int)(best_ng * ingest::kRI);
   p->nqb = nqb;
   p->decimate = (new_f == 1 && ((orig == 2 && kw == 28) || (orig == 3 && kw == 41) || (orig == 4 && kw == 54))) ? 1 : 0;
-  if (getenv("TTTS_RESAMPLE_GENERIC")) p->decimate = 0;
+  if (lab_env("TTTS_RESAMPLE_GENERIC")) p->decimate = 0;
   memset(&p->taps1, 0, sizeof(p->taps1));
   if (p->decimate) memcpy(p->taps1.t, taps, kw * sizeof(float));
   std::vector<float> t((size_t)kwp * new_pad, 0.f);
@@ -427,13 +427,13 @@ extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_
     for (int k = 0; k < kw; ++k) t[(size_t)k * new_pad + ph] = taps[(size_t)ph * kw + k];
   cudaError_t e = cudaGetDevice(&p->device);
   // tensor-core path: phases in blocks of <= 192 (multiples of 16), taps in k-steps of 8, split hi / lo
-  p->tc = (new_f >= 16 && !p->decimate && !getenv("TTTS_RESAMPLE_SIMT")) ? 1 : 0;
+  p->tc = (new_f >= 16 && !p->decimate && !lab_env("TTTS_RESAMPLE_SIMT")) ? 1 : 0;
   p->npass = (new_f + ingest::tc::kMaxNb - 1) / ingest::tc::kMaxNb;
   p->nbp = ((new_f + p->npass - 1) / p->npass + 15) / 16 * 16;
   p->ksteps = (kw + 31) / 32 * 2;                     // pairs of k-steps, rounded up to whole quads
   const size_t arr = (size_t)2 * p->nbp * 4;          // one operand array: [2 k-halves][nbp][4]
   if ((size_t)p->npass * p->ksteps * 4 * arr * sizeof(float) > kMaxTableBytes) p->tc = 0;
-  p->few = (!p->tc && !p->decimate && new_f < 16 && !getenv("TTTS_RESAMPLE_SIMT") &&
+  p->few = (!p->tc && !p->decimate && new_f < 16 && !lab_env("TTTS_RESAMPLE_SIMT") &&
             (long long)new_f * kw + kw + orig <= ingest::kMaxSmemFloats) ? 1 : 0;
   if (p->few) {
     long long fr = 2048 / new_f, cap = (ingest::kMaxSmemFloats - (long long)new_f * kw - kw - 4) / orig + 1;
@@ -571,7 +571,7 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     q.tiles_per_clip = (int)((rows_total + ingest::tc::kTileM - 1) / ingest::tc::kTileM);
     q.units = (long long)B * q.tiles_per_clip * p->npass;
     q.clip = clip; q.status = p->d_status; q.b_stages = ingest::tc::b_stages(p->nbp);
-    q.exp = getenv("TTTS_RESAMPLE_EXP") ? atoi(getenv("TTTS_RESAMPLE_EXP")) : 0;
+    q.exp = lab_env("TTTS_RESAMPLE_EXP") ? atoi(lab_env("TTTS_RESAMPLE_EXP")) : 0;
     const int grid = (int)std::min<long long>(p->num_sms, q.units);
     ingest::tc::k_resample_tc<TIn><<<grid, ingest::tc::kThreadsTc, ingest::tc::smem_bytes(p->nbp), st>>>(q);
   } else {

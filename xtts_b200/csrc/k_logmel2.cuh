@@ -90,6 +90,8 @@ struct Params {
   int passes, sp, nb, nbt, n_mels;
   float clamp, power_eps;
   int32_t* status;
+  unsigned long long* stat_ws;  // fused statistics: [2 * kMaxMels] fixed-point sums of this launch + [1] CTA ticket (zeroed by k_prep), or null
+  double* stat_acc;           // [2 * n_mels + 1] fp64, += at the end of the launch by the last CTA
   float* dbg_reim;            // optional [total_frames][2*dbg_nbt], bins dbg_kmin..
   int dbg_nbt, dbg_kmin, kmax;
   int first_k[2];             // first live bin of each parity
@@ -227,11 +229,13 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   const int park_pitch = P.n_mels + 1;
   float* s_fl = s_park + ((kTileM * park_pitch + 1) & ~1);          // [2][kChains][lo,hi][128] open pairs at chain ends
   Barriers* bars = reinterpret_cast<Barriers*>(s_fl + 2 * kChains * 2 * kTileM);
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
+  unsigned long long* s_stat = reinterpret_cast<unsigned long long*>(bars + 1);   // [2][kMaxMels] fixed-point sum | sum of squares
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_stat + 2 * kMaxMels);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- one-time setup
+  for (int i = threadIdx.x; i < 2 * kMaxMels; i += kThreads2) s_stat[i] = 0ull;
   for (int i = threadIdx.x; i < P.nbt; i += kThreads2) s_melw[i] = P.melw[i];
   for (int i = threadIdx.x; i < 2 * (P.nbt / 16); i += kThreads2) s_adv[i] = P.meladv[i];
   for (int i = threadIdx.x; i < 512; i += kThreads2) s_win[i] = P.win[i];
@@ -658,13 +662,26 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             for (int k = 0; k < 4; ++k) {
               if (32 * k < P.n_mels) {
                 const float nrm = (lane + 32 * k < P.n_mels) ? s_norm[lane + 32 * k] : 1.f, rn = 1.0f / nrm;
+                long long st_s = 0, st_q = 0;
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
                   // x / norm as reciprocal + one Newton correction: branch-free (the IEEE division's slow-path call
                   // would serialise the chains) and equal to the correctly rounded quotient except in rare last-bit ties
                   const float x = logf(fmaxf(v[i][k], P.clamp));
+                  if (P.stat_ws && rowp[i]) {
+                    // stage (4), fused: per-channel sum / sum of squares of the UN-normalised log-mel in 64-bit fixed point
+                    // (2^-32 / 2^-24 steps: every fp32 value above 2^-8 is represented exactly) -- integer addition is
+                    // associative, so the statistics are bit-identical from run to run and for any sharding of the corpus
+                    const double xd = (double)x;
+                    st_s += __double2ll_rn(xd * 4294967296.0);
+                    st_q += __double2ll_rn(xd * xd * 16777216.0);
+                  }
                   const float y = x * rn;
                   v[i][k] = fabsf(y) < 3.0e38f ? fmaf(fmaf(-y, nrm, x), rn, y) : y;   // norm 0 / inf: keep x * (1/norm)
+                }
+                if (P.stat_ws && lane + 32 * k < P.n_mels) {
+                  atomicAdd(s_stat + lane + 32 * k, (unsigned long long)st_s);
+                  atomicAdd(s_stat + kMaxMels + lane + 32 * k, (unsigned long long)st_q);
                 }
               }
             }
@@ -685,6 +702,29 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   // ---- teardown
   tc_fence_before();
   if (kPair) cluster_sync_all(); else __syncthreads();       // pair: the leader's MMAs read the peer's TMEM and smem
+  if (P.stat_ws) {
+    // this CTA's fixed-point sums -> the launch's (integer atomics: order-independent); the last CTA to arrive converts
+    // the launch totals to fp64 and adds them, with the frame count, to the caller's accumulator
+    __shared__ int s_last;
+    for (int i = threadIdx.x; i < 2 * kMaxMels; i += kThreads2)
+      if (s_stat[i]) atomicAdd(P.stat_ws + i, s_stat[i]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(P.stat_ws + 2 * kMaxMels, 1ull) == (unsigned long long)gridDim.x - 1;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      for (int i = threadIdx.x; i < 2 * P.n_mels; i += kThreads2) {
+        const bool sq = i >= P.n_mels;
+        const long long tot = (long long)atomicExch(P.stat_ws + (sq ? kMaxMels + i - P.n_mels : i), 0ull);
+        P.stat_acc[i] += (double)tot * (sq ? 1.0 / 16777216.0 : 1.0 / 4294967296.0);
+      }
+      if (threadIdx.x == 0) {
+        P.stat_acc[2 * P.n_mels] += (double)P.frame_off[P.B];
+        P.stat_ws[2 * kMaxMels] = 0ull;
+      }
+    }
+  }
   if (warp == kWarpTmem) {
     tc_fence_after();
     if (kPair) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kTmemCols) : "memory");

@@ -536,7 +536,7 @@ int vq_nearest_impl(const ttts_vq_plan* p, const float* z_rm, int64_t row_stride
   vq::Params q;
   q.zt = zt; q.pairs = p->pairs; q.npass = p->npass; q.nbp = p->nbp; q.codeB = p->d_codeB; q.ee = p->d_ee;
   q.keys = keys; q.units = l.tiles * p->npass; q.status = p->d_status;
-  q.exp = getenv("TTTS_VQ_EXP") ? atoi(getenv("TTTS_VQ_EXP")) : 0;
+  q.exp = lab_env("TTTS_VQ_EXP") ? atoi(lab_env("TTTS_VQ_EXP")) : 0;
   {
     const int grid = (int)std::min<long long>(p->num_sms, q.units);
     vq::k_vq_tc<<<grid, vq::kThreadsTc, vq::smem_bytes(p->nbp), st>>>(q);

@@ -29,6 +29,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -79,14 +81,19 @@ constexpr int kWarpEpi0 = 12;          // 4 epilogue warps: 12..15
 thread_local char g_err[512] = "";
 thread_local int g_launches = 0;
 
-// optional per-call timing of the hot kernel (library-owned CUDA event pairs, see ttts_mel_profile_*)
+// optional per-call timing of the hot kernel (plan-owned CUDA event pairs, see ttts_mel_profile_*)
 struct ProfileRing {
   cudaEvent_t* start = nullptr;
   cudaEvent_t* stop = nullptr;
-  int capacity = 0, count = 0;
+  int capacity = 0;
+  std::atomic<int> count{0};
 };
-ProfileRing g_prof;
-int g_exp_flags = 0;
+#ifdef TTTS_MEL_LAB
+std::atomic<int> g_exp_flags{0};     // lab build only (include/ttts_mel_lab.h): leg-removal timing experiments
+#define TTTS_EXP_FLAGS() g_exp_flags.load(std::memory_order_relaxed)
+#else
+#define TTTS_EXP_FLAGS() 0
+#endif
 
 int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -103,6 +110,17 @@ int fail(int code, const char* fmt, ...) {
   } while (0)
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Environment knobs (kernel selection for cross-checks, leg-removal experiments) exist in the lab build only; the
+// product library never reads the environment.
+inline const char* lab_env(const char* name) {
+#ifdef TTTS_MEL_LAB
+  return getenv(name);
+#else
+  (void)name;
+  return nullptr;
+#endif
+}
 
 }  // namespace
 
@@ -136,8 +154,10 @@ struct ttts_mel_plan {
   float2* d_melw2 = nullptr;   // [nbt2]
   uint32_t* d_meladv2 = nullptr;  // [nbt2/16], 2 bits per bin
   float* d_win2 = nullptr;     // [512]
-  int pair = 0;                // 1: CTA pairs (cta_group::2), each CTA stages half of every basis stage (TTTS_MEL_PAIR=0 disables)
+  int pair = 0;                // 1: CTA pairs (cta_group::2), each CTA stages half of every basis stage
   float* d_basis2p = nullptr;  // [2 sp][33][2 halves][4 arrays][2 k-halves][nb2/2][4]: the per-CTA half stages
+  ProfileRing prof;            // ttts_mel_profile_enable / _collect (include/ttts_mel_lab.h): measurement only
+  std::mutex prof_mu;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -191,10 +211,12 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   p->kmin = kmin;
   p->n_live = kmax - kmin + 1;
   int nb_cap = kNBMax;
-  if (const char* e = getenv("TTTS_MEL_NB_MAX")) {          // tuning knob: 96 selects double-buffered accumulators
+#ifdef TTTS_MEL_LAB
+  if (const char* e = lab_env("TTTS_MEL_NB_MAX")) {          // tuning knob: 96 selects double-buffered accumulators
     const int v = atoi(e);
     if (v >= 16 && v <= kNBMax && v % 16 == 0) nb_cap = v;
   }
+#endif
   p->passes = (p->n_live + nb_cap - 1) / nb_cap;
   p->nb = (int)align_up((size_t)((p->n_live + p->passes - 1) / p->passes), 16);
   p->nbt = p->passes * p->nb;
@@ -278,7 +300,9 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   p->sp = (n_par_max + kNBMax - 1) / kNBMax;
   p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 64);   // 4 scan chains of whole 16-bin blocks
   p->nbt2 = 2 * p->sp * p->nb2;
-  if (const char* e2 = getenv("TTTS_MEL_ALGO")) p->algo = atoi(e2) == 1 ? 1 : 2;
+#ifdef TTTS_MEL_LAB
+  if (const char* e2 = lab_env("TTTS_MEL_ALGO")) p->algo = atoi(e2) == 1 ? 1 : 2;
+#endif
   const int nb2 = p->nb2, nbt2 = p->nbt2, per_par = p->sp * p->nb2;
   std::vector<float2> melw2(nbt2, make_float2(0.f, 0.f));
   std::vector<uint32_t> meladv2(2 * (nbt2 / 16), 0u);   // [0]: single / multi close masks, [1]: 2-bit counts
@@ -355,7 +379,9 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   }
 
   p->pair = p->nb2 % 32 == 0;                 // CTA pairs by default (TTTS_MEL_PAIR=0: one CTA per tile stream)
-  if (const char* e3 = getenv("TTTS_MEL_PAIR")) p->pair = p->pair && atoi(e3) != 0;
+#ifdef TTTS_MEL_LAB
+  if (const char* e3 = lab_env("TTTS_MEL_PAIR")) p->pair = p->pair && atoi(e3) != 0;
+#endif
   std::vector<float> img2p;
   if (p->pair) {                              // same values, each stage split into the two CTAs' bin halves
     const int nh = nb2 / 2;
@@ -412,8 +438,10 @@ extern "C" int ttts_mel_plan_set_norms(ttts_mel_plan* p, const float* norms) {
   return TTTS_MEL_OK;
 }
 
+static void profile_free(ttts_mel_plan* p);
 extern "C" void ttts_mel_plan_destroy(ttts_mel_plan* p) {
   if (!p) return;
+  profile_free(p);
   cudaFree(p->d_basis); cudaFree(p->d_melw); cudaFree(p->d_meladv); cudaFree(p->d_norms);
   cudaFree(p->d_cosf); cudaFree(p->d_sinf); cudaFree(p->d_fb);
   cudaFree(p->d_basis2); cudaFree(p->d_melw2); cudaFree(p->d_meladv2); cudaFree(p->d_win2); cudaFree(p->d_basis2p);
@@ -446,6 +474,7 @@ struct Workspace {
   int32_t* n_frames;    // [B]
   float* xp;            // [B][Lp]   (k_simt and unaligned inputs only)
   float* edge;          // [B][kEdgeClip] reflect-padded samples of each clip's first and last frames
+  unsigned long long* stat;  // [2 * kMaxMels + 1] fixed-point statistics of one launch + CTA ticket (ttts_mel_forward_stats)
   int64_t Lp;
   size_t bytes;
 };
@@ -457,6 +486,7 @@ Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
   size_t off = 0;
   char* b = (char*)base;
   w.status = (int32_t*)(b + off); off += 256;
+  w.stat = (unsigned long long*)(b + off); off += align_up((size_t)(2 * kMaxMels + 1) * 8, 256);
   w.frame_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.group_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.n_frames = (int32_t*)(b + off); off += align_up((size_t)B * 4, 256);
@@ -505,7 +535,7 @@ __device__ __forceinline__ void mbar_timeout(int32_t* status, int code) {
 // completes) instead of re-issuing the probe every ~80 cycles -- ncu of round 1 showed 58 % of all issued warp
 // instructions in these loops, competing with the converter warps for issue slots.
 #ifndef TTTS_WAIT_HINT_NS
-#define TTTS_WAIT_HINT_NS 20000
+#define TTTS_WAIT_HINT_NS 0      /* measured (profiles/r2a_variants.json): no gain on V1, 2 % slower on V2 */
 #endif
 __device__ __forceinline__ uint32_t mbar_try_wait_hint(uint32_t bar, uint32_t parity) {
 #if TTTS_WAIT_HINT_NS > 0
@@ -622,7 +652,8 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
                                                const int64_t* __restrict__ lengths, int B, int64_t Lmax, int pad,
                                                int Tmax, int32_t* __restrict__ n_frames,
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
-                                               int64_t* __restrict__ group_off, int32_t* __restrict__ status) {
+                                               int64_t* __restrict__ group_off, int32_t* __restrict__ status,
+                                               unsigned long long* __restrict__ stat_ws) {
   asm volatile("griddepcontrol.launch_dependents;");   // the fused kernel may start its prologue (it waits for this grid's end)
   if (blockIdx.x > 0) {
     clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, (blockIdx.x - 1) / kPrepSplit,
@@ -632,6 +663,7 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
   __shared__ long long part[1024];
   const int tid = threadIdx.x;
   if (tid == 0) *status = 0;
+  if (stat_ws && tid <= 2 * kMaxMels) stat_ws[tid] = 0ull;
   __syncthreads();
   if (!lengths) {                           // dense batch: closed forms, no scan
     int err = 0;
@@ -1279,14 +1311,30 @@ size_t logmel2_smem_bytes(const ttts_mel_plan* p) {
   size_t s = (size_t)(p->pair ? f2::kBStagesPair * (p->nb2 / 2) : f2::kBStages2 * p->nb2) * 128 + (size_t)f2::kConvWarps2 * f2::kDepth * f2::kStageBytes +
              (size_t)p->nbt2 * sizeof(float2) + (size_t)(2 * (p->nbt2 / 16) + 4) * 4 + 512 * 4 + kMaxMels * 4 +
              (size_t)(kTileM * (p->cfg.n_mels + 1) + 2) * 4 + (size_t)2 * f2::kChains * 2 * kTileM * 4 + sizeof(f2::Barriers) + 16;
+  s += (size_t)2 * kMaxMels * 8;   // fused statistics
   return align_up(s, 16) + 1024;   // slack for the 1024 B alignment of the dynamic segment
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per function and device: raise it once (it never shrinks), not per call
+template <class Kern>
+int ensure_dynamic_smem(Kern kern, int slot, int device, size_t smem) {
+  static std::atomic<size_t> granted[8][64];
+  if (slot < 0 || slot >= 8 || device < 0 || device >= 64) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    return TTTS_MEL_OK;
+  }
+  if (granted[slot][device].load(std::memory_order_acquire) >= smem) return TTTS_MEL_OK;
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  size_t cur = granted[slot][device].load();
+  while (cur < smem && !granted[slot][device].compare_exchange_weak(cur, smem)) {}
+  return TTTS_MEL_OK;
 }
 
 enum class Impl { Tcgen05, Simt };
 
 int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, const int64_t* lengths, int32_t B,
                  int64_t Lmax, int32_t Tmax, float* out, int32_t* n_frames_user, uint8_t* mask, void* ws_ptr,
-                 size_t ws_bytes, void* stream_, Impl impl, float* dbg_reim) {
+                 size_t ws_bytes, void* stream_, Impl impl, float* dbg_reim, double* stat_acc = nullptr) {
   g_launches = 0;
   if (!p || !wav || !out || !ws_ptr) return fail(TTTS_MEL_EINVAL, "null argument");
   if (B <= 0 || Lmax <= 0 || Tmax <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d Lmax=%lld Tmax=%d)", B, (long long)Lmax, Tmax);
@@ -1306,7 +1354,8 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   // into the workspace first.
   const bool direct = impl == Impl::Tcgen05 && vec_ok && (int64_t)B * row_stride < ((int64_t)1 << 31);
   k_prep<<<kPrepSplit * B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
-                                     p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status);
+                                     p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status,
+                                     stat_acc ? w.stat : nullptr);
   ++g_launches;
   if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
@@ -1334,7 +1383,8 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.first_k[0] = p->first_k[0]; P.first_k[1] = p->first_k[1];
     for (int i = 0; i < 16; ++i) { P.cstart[i] = p->cstart[i]; P.cend[i] = p->cend[i]; }
     static_assert(f2_kChains == f2::kChains, "chain count");
-    P.exp_flags = g_exp_flags;
+    P.exp_flags = TTTS_EXP_FLAGS();
+    P.stat_ws = stat_acc ? w.stat : nullptr; P.stat_acc = stat_acc;
     const size_t smem = logmel2_smem_bytes(p);
     const bool pw1 = p->cfg.power == 1.0f;
     const bool pair = p->pair && !dbg_reim && p->num_sms >= 2;
@@ -1343,9 +1393,14 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
         dbg_reim ? (pw1 ? k_logmel2<true, true, false> : k_logmel2<false, true, false>)
         : pair   ? (pw1 ? k_logmel2<true, false, true> : k_logmel2<false, false, true>)
                  : (pw1 ? k_logmel2<true, false, false> : k_logmel2<false, false, false>);
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
-    if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
+    {
+      const int rc = ensure_dynamic_smem(kern, (dbg_reim ? 4 : pair ? 2 : 0) + (pw1 ? 1 : 0), p->device, smem);
+      if (rc != TTTS_MEL_OK) return rc;
+    }
+    ProfileRing& pr = const_cast<ttts_mel_plan*>(p)->prof;
+    const int pslot = pr.capacity > 0 ? pr.count.fetch_add(1) : -1;
+    const bool prof = pslot >= 0 && pslot < pr.capacity;
+    if (prof) cudaEventRecord(pr.start[pslot], stream);
     {
       // programmatic dependent launch behind k_prep: the prologue of the persistent kernel overlaps it
       cudaLaunchConfig_t lc{};
@@ -1359,9 +1414,10 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
       lc.attrs = at; lc.numAttrs = pair ? 2 : 1;
       CUDA_TRY(cudaLaunchKernelEx(&lc, kern, P));
     }
-    if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
+    if (prof) cudaEventRecord(pr.stop[pslot], stream);
     ++g_launches;
   } else if (impl == Impl::Tcgen05) {
+    if (stat_acc) return fail(TTTS_MEL_EINVAL, "fused statistics need the k_logmel2 kernel");
     LogmelParams P{};
     P.src = direct ? wav : w.xp; P.src_stride = direct ? row_stride : w.Lp; P.edge = w.edge;
     P.lengths = lengths; P.Lmax = Lmax; P.direct = direct; P.pad = p->cfg.pad;
@@ -1372,18 +1428,21 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
     P.frame_off = w.frame_off; P.n_frames = w.n_frames; P.B = B; P.Tmax = Tmax;
     P.out = out; P.basis = p->d_basis; P.melw = p->d_melw; P.meladv = p->d_meladv; P.norms = p->d_norms;
     P.passes = p->passes; P.nb = p->nb; P.nbt = p->nbt; P.n_mels = p->cfg.n_mels;
-    P.clamp = p->cfg.clamp; P.power_eps = p->cfg.power_eps; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim; P.exp_flags = g_exp_flags;
+    P.clamp = p->cfg.clamp; P.power_eps = p->cfg.power_eps; P.power_is_1 = p->cfg.power == 1.0f; P.status = w.status; P.dbg_reim = dbg_reim; P.exp_flags = TTTS_EXP_FLAGS();
     const size_t smem = logmel_smem_bytes(p);
     void (*kern)(const LogmelParams) =
         dbg_reim ? (P.power_is_1 ? k_logmel<true, true> : k_logmel<false, true>)
                  : (P.power_is_1 ? k_logmel<true, false> : k_logmel<false, false>);
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const bool prof = g_prof.capacity > 0 && g_prof.count < g_prof.capacity;
-    if (prof) cudaEventRecord(g_prof.start[g_prof.count], stream);
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   // lab path only
+    ProfileRing& pr = const_cast<ttts_mel_plan*>(p)->prof;
+    const int pslot = pr.capacity > 0 ? pr.count.fetch_add(1) : -1;
+    const bool prof = pslot >= 0 && pslot < pr.capacity;
+    if (prof) cudaEventRecord(pr.start[pslot], stream);
     kern<<<p->num_sms, kThreads, smem, stream>>>(P);
-    if (prof) cudaEventRecord(g_prof.stop[g_prof.count++], stream);
+    if (prof) cudaEventRecord(pr.stop[pslot], stream);
     ++g_launches;
   } else {
+    if (stat_acc) return fail(TTTS_MEL_EINVAL, "fused statistics need the k_logmel2 kernel");
     const int64_t Tall = ttts_mel_frames(p, Lmax);
     const int64_t max_frames = (int64_t)B * Tall;
     const unsigned blocks = (unsigned)((max_frames + kSimtFrames - 1) / kSimtFrames);
@@ -1410,6 +1469,18 @@ extern "C" int ttts_mel_forward(const ttts_mel_plan* p, const float* wav, int64_
                       Impl::Tcgen05, nullptr);
 }
 
+extern "C" int ttts_mel_forward_stats(const ttts_mel_plan* p, const float* wav, int64_t row_stride,
+                                      const int64_t* lengths, int32_t B, int64_t Lmax, int32_t Tmax, float* out,
+                                      int32_t* n_frames, uint8_t* mask, void* ws, size_t ws_bytes, void* stream,
+                                      double* acc) {
+  if (!acc) return fail(TTTS_MEL_EINVAL, "acc_dev is null");
+  return forward_impl(p, wav, row_stride, lengths, B, Lmax, Tmax, out, n_frames, mask, ws, ws_bytes, stream,
+                      Impl::Tcgen05, nullptr, acc);
+}
+
+extern "C" size_t ttts_mel_config_size(void) { return sizeof(ttts_mel_config); }
+
+#ifdef TTTS_MEL_LAB
 extern "C" int ttts_mel_forward_simt(const ttts_mel_plan* p, const float* wav, int64_t row_stride,
                                      const int64_t* lengths, int32_t B, int64_t Lmax, int32_t Tmax, float* out,
                                      int32_t* n_frames, uint8_t* mask, void* ws, size_t ws_bytes, void* stream) {
@@ -1425,6 +1496,8 @@ extern "C" int ttts_mel_forward_debug(const ttts_mel_plan* p, const float* wav, 
   return forward_impl(p, wav, row_stride, lengths, B, Lmax, Tmax, out, n_frames, mask, ws, ws_bytes, stream,
                       Impl::Tcgen05, reim_out);
 }
+
+#endif  // TTTS_MEL_LAB
 
 extern "C" int ttts_mel_status(const void* ws, void* stream) {
   if (!ws) return fail(TTTS_MEL_EINVAL, "null workspace");
@@ -1454,32 +1527,47 @@ extern "C" int ttts_mel_stats_accumulate(const ttts_mel_plan* p, const float* lo
 }
 
 // ------------------------------------------------------------------------------------------
-// profiling hooks: CUDA-event duration of k_logmel alone, per forward call, on the launch stream
+// measurement hooks (include/ttts_mel_lab.h): CUDA-event duration of the fused kernel alone, per forward call of ONE plan,
+// on the launch stream.  They never change what a forward computes.
 // ------------------------------------------------------------------------------------------
-extern "C" int ttts_mel_profile_enable(int32_t max_calls) {
-  for (int i = 0; i < g_prof.capacity; ++i) { cudaEventDestroy(g_prof.start[i]); cudaEventDestroy(g_prof.stop[i]); }
-  delete[] g_prof.start; delete[] g_prof.stop;
-  g_prof = ProfileRing();
+static void profile_free(ttts_mel_plan* p) {
+  for (int i = 0; i < p->prof.capacity; ++i) { cudaEventDestroy(p->prof.start[i]); cudaEventDestroy(p->prof.stop[i]); }
+  delete[] p->prof.start; delete[] p->prof.stop;
+  p->prof.start = p->prof.stop = nullptr;
+  p->prof.capacity = 0;
+  p->prof.count.store(0);
+}
+
+extern "C" int ttts_mel_profile_enable(ttts_mel_plan* p, int32_t max_calls) {
+  if (!p) return fail(TTTS_MEL_EINVAL, "null plan");
+  std::lock_guard<std::mutex> lk(p->prof_mu);
+  profile_free(p);
   if (max_calls <= 0) return TTTS_MEL_OK;
-  g_prof.start = new cudaEvent_t[max_calls];
-  g_prof.stop = new cudaEvent_t[max_calls];
+  p->prof.start = new cudaEvent_t[max_calls];
+  p->prof.stop = new cudaEvent_t[max_calls];
   for (int i = 0; i < max_calls; ++i) {
-    CUDA_TRY(cudaEventCreate(&g_prof.start[i]));
-    CUDA_TRY(cudaEventCreate(&g_prof.stop[i]));
+    CUDA_TRY(cudaEventCreate(&p->prof.start[i]));
+    CUDA_TRY(cudaEventCreate(&p->prof.stop[i]));
   }
-  g_prof.capacity = max_calls;
+  p->prof.capacity = max_calls;
   return TTTS_MEL_OK;
 }
 
-extern "C" int ttts_mel_profile_collect(float* ms_out, int32_t capacity) {
+extern "C" int ttts_mel_profile_collect(ttts_mel_plan* p, float* ms_out, int32_t capacity) {
+  if (!p || !ms_out) return fail(TTTS_MEL_EINVAL, "null argument");
+  std::lock_guard<std::mutex> lk(p->prof_mu);
   CUDA_TRY(cudaDeviceSynchronize());
-  const int n = g_prof.count < capacity ? g_prof.count : capacity;
-  for (int i = 0; i < n; ++i) CUDA_TRY(cudaEventElapsedTime(&ms_out[i], g_prof.start[i], g_prof.stop[i]));
-  g_prof.count = 0;
+  int n = p->prof.count.load();
+  if (n > p->prof.capacity) n = p->prof.capacity;
+  if (n > capacity) n = capacity;
+  for (int i = 0; i < n; ++i) CUDA_TRY(cudaEventElapsedTime(&ms_out[i], p->prof.start[i], p->prof.stop[i]));
+  p->prof.count.store(0);
   return n;
 }
 
-extern "C" void ttts_mel_set_experiment(int32_t flags) { g_exp_flags = flags; }
+#ifdef TTTS_MEL_LAB
+extern "C" void ttts_mel_set_experiment(int32_t flags) { g_exp_flags.store(flags); }
+#endif
 
 // ------------------------------------------------------------------------------------------
 // ingestion in front of the path (int16 PCM -> float32, sinc resample): include/ttts_ingest.h

@@ -127,11 +127,12 @@ class Resampler:
         taps, self.orig, self.new, self.width = sinc_resample_taps(orig_freq, new_freq, lowpass_filter_width,
                                                                    rolloff, kernel_dtype)
         self.taps = taps
+        self._lib = _cabi.lib()          # the library this plan lives in (tests may select the lab build)
         self._h = None
         import ctypes
         h = ctypes.c_void_p()
         with torch.cuda.device(self.device):
-            _cabi.check(_cabi.lib().ttts_resample_plan_create(taps.data_ptr(), self.orig, self.new, self.width,
+            _cabi.check(self._lib.ttts_resample_plan_create(taps.data_ptr(), self.orig, self.new, self.width,
                                                               ctypes.byref(h)))
         self._h = h
 
@@ -139,7 +140,7 @@ class Resampler:
         h, self._h = getattr(self, "_h", None), None
         if h:
             try:
-                _cabi.lib().ttts_resample_plan_destroy(h)
+                self._lib.ttts_resample_plan_destroy(h)
             except Exception:
                 pass
 
@@ -175,7 +176,7 @@ class Resampler:
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
             row_stride = int(x.stride(0)) if B > 1 else L
-            _cabi.check(_cabi.lib().ttts_resample_forward(
+            _cabi.check(self._lib.ttts_resample_forward(
                 self._h, x.data_ptr(), row_stride, len_dev.data_ptr() if len_dev is not None else None, B, L,
                 out.data_ptr(), self._row_stride(out), 1 if clip else 0, stream))
         if squeeze:
@@ -201,7 +202,7 @@ class Resampler:
         out = self._alloc(B, self.out_len(F))
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            _cabi.check(_cabi.lib().ttts_resample_pcm16_forward(
+            _cabi.check(self._lib.ttts_resample_pcm16_forward(
                 self._h, pcm.data_ptr(), F * C, C, fr.data_ptr() if fr is not None else None, B, F,
                 out.data_ptr(), self._row_stride(out), 1 if clip else 0, stream))
         if fr is not None:

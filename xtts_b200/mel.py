@@ -48,7 +48,10 @@ class MelPlan:
                  n_mels: int, f_min: float, f_max: Optional[float], power: float, norm: Optional[str],
                  mel_scale: str = "htk", normalized: bool = False, clamp: float = 1e-5,
                  center: bool = True, pre_pad: int = 0, power_eps: float = 0.0,
-                 fb: Optional[torch.Tensor] = None, device: Union[str, torch.device, int] = "cuda"):
+                 fb: Optional[torch.Tensor] = None, device: Union[str, torch.device, int] = "cuda",
+                 lab: bool = False):
+        self._lib = _cabi.lab() if lab else _cabi.lib()      # lab: tests/tools only (include/ttts_mel_lab.h)
+        self.lab = bool(lab)
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("MelPlan needs a CUDA device (sm_100a); there is no CPU fallback")
@@ -69,19 +72,19 @@ class MelPlan:
                               float(power_eps))
         handle = ctypes.c_void_p()
         with torch.cuda.device(self.device):
-            _cabi.check(_cabi.lib().ttts_mel_plan_create(ctypes.byref(cfg), self.fb.data_ptr(),
-                                                         self.window.data_ptr(), ctypes.byref(handle)))
+            _cabi.check(self._lib.ttts_mel_plan_create(ctypes.byref(cfg), self.fb.data_ptr(),
+                                                       self.window.data_ptr(), ctypes.byref(handle)))
         self._h = handle
-        self.first_bin = int(_cabi.lib().ttts_mel_first_bin(self._h))
-        self.num_bins = int(_cabi.lib().ttts_mel_num_bins(self._h))
-        self.live_bins = int(_cabi.lib().ttts_mel_live_bins(self._h))
+        self.first_bin = int(self._lib.ttts_mel_first_bin(self._h))
+        self.num_bins = int(self._lib.ttts_mel_num_bins(self._h))
+        self.live_bins = int(self._lib.ttts_mel_live_bins(self._h))
         self.last_launches = 0
 
     def __del__(self):
         h = getattr(self, "_h", None)
         if h:
             try:
-                _cabi.lib().ttts_mel_plan_destroy(h)
+                self._lib.ttts_mel_plan_destroy(h)
             except Exception:
                 pass
             self._h = None
@@ -89,14 +92,14 @@ class MelPlan:
     def set_norms(self, norms: Optional[torch.Tensor]) -> None:
         with torch.cuda.device(self.device):
             if norms is None:
-                _cabi.check(_cabi.lib().ttts_mel_plan_set_norms(self._h, None))
+                _cabi.check(self._lib.ttts_mel_plan_set_norms(self._h, None))
                 return
             host = norms.detach().to("cpu", torch.float32).contiguous()
             if host.numel() != self.n_mels:
                 raise ValueError(f"mel_norms has {host.numel()} entries, expected {self.n_mels}")
             # the plan is read by kernels already in flight on this device's streams
             torch.cuda.synchronize(self.device)
-            _cabi.check(_cabi.lib().ttts_mel_plan_set_norms(self._h, host.data_ptr()))
+            _cabi.check(self._lib.ttts_mel_plan_set_norms(self._h, host.data_ptr()))
 
     def frames(self, length: int) -> int:
         """torch.stft frame count; raises like F.pad(mode='reflect') when the clip is too short."""
@@ -107,9 +110,12 @@ class MelPlan:
         return 1 + (length + 2 * self.pad - self.n_fft) // self.hop
 
     def forward(self, wav: torch.Tensor, lengths: Optional[torch.Tensor] = None, *, want_mask: bool = False,
-                impl: str = "tcgen05", debug_reim: bool = False, t_max: Optional[int] = None):
+                impl: str = "tcgen05", debug_reim: bool = False, t_max: Optional[int] = None,
+                stats_acc: Optional[torch.Tensor] = None):
         """wav [B, L] fp32 CUDA (last dim contiguous).  Returns (mel_btc [B, T, n_mels] fp32,
-        n_frames [B] int32, mask [B, T] uint8 | None[, reim])."""
+        n_frames [B] int32, mask [B, T] uint8 | None[, reim]).  ``stats_acc`` (fp64 [2*n_mels+1], device): the
+        per-channel statistics of this batch's un-normalised log-mel are added to it inside the same kernel
+        (``ttts_mel_forward_stats``)."""
         if wav.device != self.device:
             raise RuntimeError(f"input on {wav.device}, plan on {self.device}")
         if wav.dtype != torch.float32 or wav.dim() != 2:
@@ -120,7 +126,7 @@ class MelPlan:
         if B == 0:
             raise RuntimeError("empty batch")
         T = self.frames(Lmax) if t_max is None else int(t_max)
-        lib = _cabi.lib()
+        lib = self._lib
         len_dev = None
         if lengths is not None:
             len_dev = lengths.to(device=self.device, dtype=torch.int64).contiguous()
@@ -142,10 +148,20 @@ class MelPlan:
             if debug_reim:
                 total = B * self.frames(Lmax)
                 reim = torch.zeros((total, 2 * self.num_bins), dtype=torch.float32, device=self.device)
+                if not self.lab:
+                    raise RuntimeError("the DFT-stage dump exists in the lab build only: MelPlan(..., lab=True)")
                 _cabi.check(lib.ttts_mel_forward_debug(*args, reim.data_ptr()))
+            elif stats_acc is not None:
+                if impl != "tcgen05":
+                    raise ValueError("fused statistics run on the tcgen05 kernel only")
+                assert stats_acc.dtype == torch.float64 and stats_acc.numel() == 2 * self.n_mels + 1 \
+                    and stats_acc.is_contiguous() and stats_acc.device == self.device
+                _cabi.check(lib.ttts_mel_forward_stats(*args, stats_acc.data_ptr()))
             elif impl == "tcgen05":
                 _cabi.check(lib.ttts_mel_forward(*args))
             elif impl == "simt":
+                if not self.lab:
+                    raise RuntimeError("the CUDA-core cross-check kernel exists in the lab build only: MelPlan(..., lab=True)")
                 _cabi.check(lib.ttts_mel_forward_simt(*args))
             else:
                 raise ValueError(f"unknown impl {impl!r}")
@@ -162,7 +178,18 @@ class MelPlan:
             return
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            _cabi.check(_cabi.lib().ttts_mel_status(ws.data_ptr(), stream))
+            _cabi.check(self._lib.ttts_mel_status(ws.data_ptr(), stream))
+
+    def profile_enable(self, max_calls: int) -> None:
+        """Measurement hook (include/ttts_mel_lab.h): time the fused kernel of the next ``max_calls`` forwards of this plan."""
+        _cabi.check(self._lib.ttts_mel_profile_enable(self._h, int(max_calls)))
+
+    def profile_collect(self, capacity: int):
+        buf = (ctypes.c_float * int(capacity))()
+        n = int(self._lib.ttts_mel_profile_collect(self._h, buf, int(capacity)))
+        if n < 0:
+            _cabi.check(n)
+        return [float(buf[i]) for i in range(n)]
 
     def stats_accumulate(self, logmel_btc: torch.Tensor, n_frames: torch.Tensor, acc: torch.Tensor) -> None:
         """acc[2*n_mels+1] (fp64, device) += [sum | sumsq | count] of un-normalised log-mel."""
@@ -171,7 +198,7 @@ class MelPlan:
         nf = n_frames.to(device=self.device, dtype=torch.int32).contiguous()
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            _cabi.check(_cabi.lib().ttts_mel_stats_accumulate(
+            _cabi.check(self._lib.ttts_mel_stats_accumulate(
                 self._h, logmel_btc.data_ptr(), nf.data_ptr(), int(logmel_btc.shape[0]), int(logmel_btc.shape[1]),
                 acc.data_ptr(), stream))
 
@@ -199,6 +226,30 @@ class _MelModuleBase(nn.Module):
             plan.set_norms(norms)
             plan._norms_key = nkey
         return plan
+
+    # The cached plans hold library handles (ctypes pointers): a copy / pickle of the module (EMA copies, torch.save(model),
+    # spawn workers -- the reference module supports all of them) drops them and rebuilds lazily.
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        state.pop("_plans", None)
+        return state
+
+    def __deepcopy__(self, memo):
+        import copy
+        new = self.__class__.__new__(self.__class__)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            if k != "_plans":
+                new.__dict__[k] = copy.deepcopy(v, memo)
+        return new
+
+    def status(self, device=None) -> None:
+        """Synchronise and raise if the last forward on ``device`` reported a device-side error.  With ``lengths`` given
+        as a CUDA tensor nothing is validated on the host (no sync in ``forward``): a clip that is too short or longer
+        than the batch width yields all-zero rows and is reported here (the reference raises inside its call)."""
+        for key, plan in self.__dict__.get("_plans", {}).items():
+            if device is None or torch.device(*key) == torch.device(device):
+                plan.status()
 
     def _run(self, inp: torch.Tensor, lengths=None, impl: str = "tcgen05"):
         if len(inp.shape) == 3:   # squeeze the channel dimension (mono), utils.py:510-511

@@ -89,19 +89,23 @@ def norms_from_stats(acc: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     also returns the per-channel standard deviation."""
     n = (acc.numel() - 1) // 2
     cnt = acc[2 * n]
+    if float(cnt) <= 0:
+        raise ValueError("mel_norms statistics are empty (no valid frame was accumulated)")
     mean = acc[:n] / cnt
     var = (acc[n:2 * n] / cnt - mean * mean).clamp_min(0)
     return mean.to(torch.float32), var.sqrt().to(torch.float32)
 
 
 class MelSweep:
-    """Two-pass sweep of a corpus: pass 1 accumulates statistics, all-reduces them and derives mel_norms;
-    pass 2 (or any later ``TorchMelSpectrogram`` call) applies them.
+    """Two-pass sweep of a corpus: pass 1 (``run_stats``) accumulates the per-channel statistics inside the log-mel
+    kernel (``ttts_mel_forward_stats``), all-reduces them and derives mel_norms; pass 2 (``run_files``, or any later
+    ``TorchMelSpectrogram`` call) applies them and writes the files.
 
     ``fetch(indices, max_len) -> (wav[B, max_len] float32 CUDA tensor, lengths[B] int64)`` supplies a batch;
     ``sink(indices, mel[B, n_mels, T], n_frames[B])`` consumes results (the reference's per-file
     ``torch.save(mel, f'{wav}.mel.pth')``, mel_extract.py:27); ``done(index) -> bool`` is the reference's
-    skip-if-exists resume rule (mel_extract.py:10-12).
+    skip-if-exists resume rule (mel_extract.py:10-12).  ``done`` only gates the SINK: the statistics always cover
+    the whole corpus, so a resumed sweep derives the same mel_norms as an uninterrupted one.
 
     ``bucket_seconds`` bounds the length spread inside a batch.  It only bounds MEMORY (the padded input tensor):
     the kernel indexes frames of all clips in one flat space, so padding costs no compute, and larger batches fill
@@ -121,11 +125,39 @@ class MelSweep:
     def my_buckets(self) -> List[Bucket]:
         return [self.buckets[j] for j in self.owned[self.rank]]
 
+    def _set_norms(self, norms) -> None:
+        # the plan may belong to a module (mod._plan_for(dev)): invalidate the module's cache key so that its next call
+        # re-uploads ITS norms instead of trusting what the sweep left in the plan
+        self.plan.set_norms(norms)
+        self.plan._norms_key = ("sweep", id(self))
+
     def run_stats(self, fetch: Callable, done: Optional[Callable[[int], bool]] = None,
-                  sink: Optional[Callable] = None) -> torch.Tensor:
-        """Pass 1 on this rank's buckets; returns the all-reduced statistics (identical on every rank)."""
+                  sink: Optional[Callable] = None, *, fused: bool = True) -> torch.Tensor:
+        """Pass 1 on this rank's buckets; returns the all-reduced statistics (identical on every rank).
+        ``sink`` (optional) receives the UN-normalised log-mel of the clips that are not ``done``."""
         acc = torch.zeros(2 * self.plan.n_mels + 1, dtype=torch.float64, device=self.plan.device)
-        self.plan.set_norms(None)
+        self._set_norms(None)
+        for b in self.my_buckets():
+            idx = list(b.indices)
+            wav, lens = fetch(idx, b.max_len)
+            t_max = self.plan.frames(int(max(self.lengths[i] for i in idx)))
+            if fused:
+                mel, n_frames, _ = self.plan.forward(wav, lens, t_max=t_max, stats_acc=acc)
+            else:
+                mel, n_frames, _ = self.plan.forward(wav, lens, t_max=t_max)
+                self.plan.stats_accumulate(mel, n_frames, acc)
+            if sink is not None:
+                self._sink_not_done(sink, done, idx, mel, n_frames)
+        if sink is not None and hasattr(sink, "flush"):
+            sink.flush()
+        return allreduce_stats(acc)
+
+    def run_files(self, fetch: Callable, sink: Callable, done: Optional[Callable[[int], bool]] = None,
+                  norms: Optional[torch.Tensor] = None) -> int:
+        """Pass 2: apply ``norms`` (None: un-normalised, what MelSpectrogramFeatures writes) and hand every clip that is
+        not ``done`` to ``sink``; batches whose clips are all done are not even fetched.  Returns the clips written."""
+        self._set_norms(norms)
+        written = 0
         for b in self.my_buckets():
             idx = [i for i in b.indices if not (done and done(i))]
             if not idx:
@@ -133,27 +165,122 @@ class MelSweep:
             wav, lens = fetch(idx, b.max_len)
             t_max = self.plan.frames(int(max(self.lengths[i] for i in idx)))
             mel, n_frames, _ = self.plan.forward(wav, lens, t_max=t_max)
-            self.plan.stats_accumulate(mel, n_frames, acc)
-            if sink is not None:
-                sink(idx, mel.transpose(1, 2), n_frames)
-        return allreduce_stats(acc)
+            sink(idx, mel.transpose(1, 2), n_frames)
+            written += len(idx)
+        if hasattr(sink, "flush"):
+            sink.flush()
+        return written
+
+    @staticmethod
+    def _sink_not_done(sink, done, idx, mel, n_frames) -> None:
+        keep = [k for k, i in enumerate(idx) if not (done and done(i))]
+        if not keep:
+            return
+        if len(keep) == len(idx):
+            sink(idx, mel.transpose(1, 2), n_frames)
+        else:
+            sel = torch.as_tensor(keep, device=mel.device)
+            sink([idx[k] for k in keep], mel.index_select(0, sel).transpose(1, 2), n_frames.index_select(0, sel))
 
 
-def mel_pth_sink(paths: Sequence[str], suffix: str = ".mel.pth") -> Callable:
+class _AsyncWriter:
+    """One writer thread behind a bounded queue: the device->host copy of batch i and its ``torch.save`` calls overlap
+    the kernels of batch i+1 (the reference does a blocking ``mel.cpu()`` + ``torch.save`` per clip, mel_extract.py:27)."""
+
+    def __init__(self, depth: int = 3):
+        import queue
+        import threading
+        self.q = queue.Queue(maxsize=depth)
+        self.err = None
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def _run(self):
+        while True:
+            job = self.q.get()
+            try:
+                if job is None:
+                    return
+                event, fn = job
+                if event is not None:
+                    event.synchronize()
+                if self.err is None:
+                    fn()
+            except BaseException as e:      # surfaced by flush()
+                self.err = e
+            finally:
+                self.q.task_done()
+
+    def submit(self, event, fn) -> None:
+        if self.err is not None:
+            self.flush()
+        self.q.put((event, fn))
+
+    def flush(self) -> None:
+        self.q.join()
+        if self.err is not None:
+            e, self.err = self.err, None
+            raise e
+
+
+def _save_atomic(obj, out: str) -> None:
+    import os
+    tmp = out + ".tmp"
+    torch.save(obj, tmp)
+    os.replace(tmp, out)         # a killed sweep never leaves a truncated file for the resume rule to skip
+
+
+def mel_pth_sink(paths: Sequence[str], suffix: str = ".mel.pth", *, overlap: bool = True) -> Callable:
     """``sink`` that writes what ``process_mel`` writes (mel_extract.py:9,26-27): one file ``<wav path>.mel.pth``
     per clip holding ``torch.save`` of a CPU float32 tensor ``[1, n_mels, T]`` (that clip's frames only).  One
-    device->host copy per batch; the per-file slices are views of it."""
-    import os
+    device->host copy per batch into a pooled pinned buffer on a side stream; the per-file slices and the
+    ``torch.save`` calls run on a writer thread (``overlap=False``: everything inline).  ``sink.flush()`` waits for the
+    files (MelSweep calls it at the end of a pass)."""
+    writer = _AsyncWriter() if overlap else None
+    pool: List[torch.Tensor] = []
+    side = {}
+
+    def write(host, counts, indices):
+        for b, i in enumerate(indices):
+            _save_atomic(host[b:b + 1, :, :counts[b]].contiguous().clone(), paths[i] + suffix)
 
     def sink(indices, mel_bct: torch.Tensor, n_frames: torch.Tensor) -> None:
-        host = mel_bct.to("cpu", non_blocking=False)
-        counts = n_frames.to("cpu").tolist()
-        for b, i in enumerate(indices):
-            out = paths[i] + suffix
-            tmp = out + ".tmp"
-            torch.save(host[b:b + 1, :, :counts[b]].contiguous().clone(), tmp)
-            os.replace(tmp, out)         # a killed sweep never leaves a truncated file for the resume rule to skip
+        if writer is None or not mel_bct.is_cuda:
+            write(mel_bct.to("cpu"), n_frames.to("cpu").tolist(), list(indices))
+            return
+        dev = mel_bct.device
+        if dev not in side:
+            side[dev] = torch.cuda.Stream(dev)
+        B, C, T = mel_bct.shape
+        need = B * C * T
+        buf = None
+        for k, t in enumerate(pool):
+            if t.numel() >= need:
+                buf = pool.pop(k)
+                break
+        if buf is None:
+            buf = torch.empty(need, dtype=torch.float32, pin_memory=True)
+        cnt = torch.empty(B, dtype=n_frames.dtype, pin_memory=True)
+        host = buf[:need].view(B, T, C)
+        cur = torch.cuda.current_stream(dev)
+        s = side[dev]
+        s.wait_stream(cur)
+        with torch.cuda.stream(s):
+            host.copy_(mel_bct.transpose(1, 2), non_blocking=True)      # the physical [B, T, C] layout: one flat copy
+            cnt.copy_(n_frames, non_blocking=True)
+            mel_bct.record_stream(s)
+            n_frames.record_stream(s)
+            ev = torch.cuda.Event()
+            ev.record(s)
+        idx = list(indices)
 
+        def job():
+            write(host.transpose(1, 2), cnt.tolist(), idx)
+            pool.append(buf)
+
+        writer.submit(ev, job)
+
+    sink.flush = (writer.flush if writer is not None else (lambda: None))
     return sink
 
 
@@ -183,10 +310,7 @@ def melvq_pth_sink(paths: Sequence[str], encode: Callable, codebook, suffix: str
         codes = search(logits).to("cpu")
         counts = [int(c) for c in (n_tokens.tolist() if torch.is_tensor(n_tokens) else n_tokens)]
         for b, i in enumerate(indices):
-            out = paths[i] + suffix
-            tmp = out + ".tmp"
-            torch.save(codes[b:b + 1, :counts[b]].tolist(), tmp)
-            os.replace(tmp, out)
+            _save_atomic(codes[b:b + 1, :counts[b]].tolist(), paths[i] + suffix)
 
     return sink
 

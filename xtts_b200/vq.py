@@ -37,17 +37,18 @@ class VQPlan:
         self.device = device
         self.dim, self.n_embed = (int(s) for s in embed.shape)
         host = embed.detach().to(device="cpu", dtype=torch.float32).contiguous()
+        self._lib = _cabi.lib()          # the library this plan lives in (tests may select the lab build)
         self._h = None
         h = ctypes.c_void_p()
         with torch.cuda.device(device):
-            _cabi.check(_cabi.lib().ttts_vq_plan_create(host.data_ptr(), self.dim, self.n_embed, ctypes.byref(h)))
+            _cabi.check(self._lib.ttts_vq_plan_create(host.data_ptr(), self.dim, self.n_embed, ctypes.byref(h)))
         self._h = h
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
             try:
-                _cabi.lib().ttts_vq_plan_destroy(h)
+                self._lib.ttts_vq_plan_destroy(h)
             except Exception:
                 pass
 
@@ -68,7 +69,7 @@ class VQPlan:
         n = int(flat.shape[0])
         if n == 0:
             raise RuntimeError("empty input")
-        lib = _cabi.lib()
+        lib = self._lib
         with torch.cuda.device(self.device):
             ind = torch.empty(n, dtype=torch.int64, device=self.device)
             quant = torch.empty((n, self.dim), dtype=torch.float32, device=self.device) if want_quantize else None
@@ -98,7 +99,7 @@ class VQPlan:
             raise RuntimeError("empty input")
         if z.stride(2) != 1 or z.stride(1) < T or z.stride(0) < z.stride(1) * self.dim:
             z = z.contiguous()
-        lib = _cabi.lib()
+        lib = self._lib
         with torch.cuda.device(self.device):
             ind = torch.empty((B, T), dtype=torch.int64, device=self.device)
             ws_bytes = int(lib.ttts_vq_workspace_bytes(self._h, B * T))
@@ -119,13 +120,13 @@ class VQPlan:
         with torch.cuda.device(self.device):
             out = torch.empty((n, self.dim), dtype=torch.float32, device=self.device)
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            _cabi.check(_cabi.lib().ttts_vq_embed_code(self._h, ids.data_ptr(), n, out.data_ptr(), self.dim, stream))
+            _cabi.check(self._lib.ttts_vq_embed_code(self._h, ids.data_ptr(), n, out.data_ptr(), self.dim, stream))
         return out.view(*embed_id.shape, self.dim)
 
     def status(self) -> None:
         """Synchronise and raise if a kernel of this plan flagged an error (tests; optional for callers)."""
         with torch.cuda.device(self.device):
-            _cabi.check(_cabi.lib().ttts_vq_status(self._h, torch.cuda.current_stream(self.device).cuda_stream))
+            _cabi.check(self._lib.ttts_vq_status(self._h, torch.cuda.current_stream(self.device).cuda_stream))
 
 
 class Quantize(nn.Module):
