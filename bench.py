@@ -608,6 +608,21 @@ def run_ours(args):
     h2d_gbs = copy_gbs(dev_f32[0], host_f32[0])
     barrier()
     d2h_gbs = copy_gbs(host_f32[1], dev_f32[1])
+    # both directions at once (what the e2e loop does: H2D of step i+1 while step i-1 drains), rank 0's share
+    barrier()
+    def duplex():
+        with torch.cuda.stream(copy_s):
+            dev_f32[0].copy_(host_f32[0], non_blocking=True)
+        with torch.cuda.stream(out_s):
+            host_f32[1].copy_(dev_f32[1], non_blocking=True)
+    for _ in range(3):
+        duplex()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        duplex()
+    torch.cuda.synchronize(dev)
+    duplex_gbs = 20 * B_CLIPS * CLIP_LEN * 4 / (time.perf_counter() - t0) / 1e9
     del host_f32, dev_f32
     # the same loop fed with what a 16-bit WAV at the target rate holds: pinned int16 -> H2D -> decode_pcm16 (k_pcm16)
     # -> the same mel call -> D2H
@@ -669,6 +684,7 @@ def run_ours(args):
                            "max over ranks",
                     "numa": numa, "max_abs_diff_vs_resident": chk,
                     "host_limiter": {"pinned_h2d_GB/s": h2d_gbs, "pinned_d2h_GB/s": d2h_gbs,
+                                     "duplex_GB/s_each_way": duplex_gbs,
                                      "copy_bound_audio_s_per_s_per_gpu": audio_step / (B_CLIPS * CLIP_LEN * 4 / (h2d_gbs * 1e9)),
                                      "note": "rank 0's rate while every rank copies at once, one direction at a time; the "
                                              "step's H2D copy alone bounds e2e"}},
@@ -677,6 +693,7 @@ def run_ours(args):
                           "how": "the e2e loop fed with pinned int16 mono PCM at 22050 Hz (what a WAV holds): H2D -> "
                                  "decode_pcm16 -> TorchMelSpectrogram.forward -> D2H",
                           "copy_bound_audio_s_per_s_per_gpu": audio_step / (B_CLIPS * CLIP_LEN * 2 / (h2d_gbs * 1e9)),
+                          "copy_bound_duplex": audio_step / (B_CLIPS * CLIP_LEN * 2 / (duplex_gbs * 1e9)),
                           "max_abs_diff_vs_resident": chk_pcm},
             "gpu_launches": launches,
             "kernels_per_step": {"k_prep(+edge buffers)": 1, "k_logmel2": 1},
