@@ -27,7 +27,11 @@
 namespace f2 {
 
 constexpr int kSets = 3;                         // converter sets: set s serves the k-steps with sequence number == s (mod 3)
-constexpr int kAStages2 = 4;                     // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
+constexpr int kAStages2 = 8;                     // most A-operand TMEM stages (32 columns each): the ring takes what the accumulators
+                                                 // leave of the 512 columns -- 4 stages behind 2 x 192 bins (V1), 8 behind 2 x 128 (V2)
+#ifndef F2_ASTAGES_MAX
+#define F2_ASTAGES_MAX 8
+#endif
 constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
 constexpr int kSlotFloats = 20;                  // 12 forward taps + 8 mirrored taps; 80 B pitch: conflict-free LDS.128
@@ -55,18 +59,38 @@ constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
 #endif
 constexpr int kRegsMisc = F2_REGS_MISC, kRegsConv = F2_REGS_CONV, kRegsEpi = F2_REGS_EPI;
 static_assert(128 * kRegsMisc + 384 * kRegsConv + 512 * kRegsEpi <= 65536, "register budgets exceed the file");
+// magnitude (power 1) instantiations: the epilogue holds its chain's last 32 bins as power values in registers and hands
+// the accumulators back before scanning them (measured, profiles/r2e_variants_hold_sqrt.txt: V2 -3 %, V1 +1.6 %: V1 keeps
+// the streaming scan and round 1's budgets)
+#ifndef F2_REGS_CONV_P1
+#define F2_REGS_CONV_P1 80
+#endif
+#ifndef F2_REGS_EPI_P1
+#define F2_REGS_EPI_P1 56
+#endif
+#ifndef F2_HOLD_P1
+#define F2_HOLD_P1 32
+#endif
+static_assert(128 * kRegsMisc + 384 * F2_REGS_CONV_P1 + 512 * F2_REGS_EPI_P1 <= 65536, "register budgets exceed the file");
 constexpr int kBStages2 = 4;                      // basis ring depth (single CTA: 4 x 24 KB)
 #ifndef F2_BSTAGES_PAIR
 #define F2_BSTAGES_PAIR 8
 #endif
 constexpr int kBStagesPair = F2_BSTAGES_PAIR;     // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
-constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
 constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
 #ifndef F2_QR_UNROLL
 #define F2_QR_UNROLL 1
 #endif
 constexpr int kQrUnroll = F2_QR_UNROLL;          // unrolling of the epilogue's 4-bin rounds
 constexpr int kGroup = 32;                       // frames per group (one converter / epilogue warp)
+#ifndef F2_HOLD
+#define F2_HOLD 0
+#endif
+
+#ifndef F2_SQRT_APPROX
+#define F2_SQRT_APPROX 1
+#endif
+static_assert(F2_HOLD % 16 == 0 && F2_HOLD >= 0 && F2_HOLD <= 48 && F2_HOLD_P1 % 16 == 0 && F2_HOLD_P1 <= 48, "F2_HOLD");
 
 struct Params {
   const float* src;           // direct: the caller's waveform [B][src_stride]; else workspace xp [B][Lp]
@@ -212,6 +236,8 @@ template <bool kPower1, bool kDebug, bool kPair>
 __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P) {
   using namespace f2;
   constexpr int kBS = kPair ? kBStagesPair : kBStages2;    // basis ring depth
+  constexpr int kRegsConvT = kPower1 ? F2_REGS_CONV_P1 : kRegsConv, kRegsEpiT = kPower1 ? F2_REGS_EPI_P1 : kRegsEpi;
+  constexpr int kHold = kPower1 ? F2_HOLD_P1 : F2_HOLD;    // trailing bins of an epilogue chain held in registers
   extern __shared__ __align__(1024) uint8_t smem[];
   // ---- carve shared memory
   const int nb = P.nb;
@@ -266,6 +292,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   if (kPair) cluster_sync_all(); else __syncthreads();       // pair: the peer's barriers must exist before anyone arrives on them
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
+  // TMEM columns: Re [0, nb) | Im [nb, 2 nb) | A ring from 2 nb on (a power-of-two number of 32-column stages)
+  const uint32_t col_a = 2u * (uint32_t)nb;
+  const uint32_t a_stages = (512u - col_a) / 32u >= 8u && F2_ASTAGES_MAX >= 8 ? 8u : 4u, a_shift = a_stages == 8u ? 3u : 2u;
   const int64_t total_groups = P.group_off[P.B];
   const int num_tiles = (int)((total_groups + 3) / 4);
   // a pair walks tiles (2j, 2j+1) in lock step: both CTAs run the same number of iterations, a missing odd tile is empty
@@ -312,7 +341,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t desc_lo0 = (((uint32_t)nbh * 16u) >> 4) << 16;  // LBO = nbh*16 B between the two k-halves
     const uint32_t arr16 = ((uint32_t)nbh * 32u) >> 4;          // one operand array, in 16 B units
     const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
-    const uint32_t d_re = tmem, d_im = tmem + kNBMax;
+    const uint32_t d_re = tmem, d_im = tmem + (uint32_t)nb;
     uint32_t kseq = 0, pseq = 0;
     uint32_t as = 0, ause = 0;                                   // A stage = kseq % kAStages2, its use count
     for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
@@ -333,7 +362,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           }
           tc_fence_after();
           if (elect_one_sync()) {
-            const uint32_t a_base = tmem + kColA2 + as * 32;
+            const uint32_t a_base = tmem + col_a + as * 32;
             const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
             const uint64_t c_hi = ((uint64_t)desc_hi << 32) | lo;
             const uint64_t c_lo = ((uint64_t)desc_hi << 32) | (lo + arr16);
@@ -362,13 +391,13 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             if (ks == kKS - 1) commit(smem_u32(&bars->acc_full));
           }
           __syncwarp();
-          if (++as == kAStages2) { as = 0; ++ause; }
+          if (++as == a_stages) { as = 0; ++ause; }
         }
       }
     }
   }
   } else if (wgroup <= kSets) {
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsConv));
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsConvT));
   if (!(P.exp_flags & 1)) {
     // ===== converters: stage own slots (cp.async) -> window + double fold + TF32 split -> TMEM A stage `set` =====
     const float *src_p = P.src, *edge_p = P.edge;
@@ -517,8 +546,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       }
       __syncwarp();                                    // every lane has its taps in registers: the stage can be refilled
       issue(stage);
-      const uint32_t as = kseq % kAStages2, ause = kseq / kAStages2;
-      const uint32_t a_base = tmem + lane_addr + kColA2 + as * 32;
+      const uint32_t as = kseq & (a_stages - 1u), ause = kseq >> a_shift;
+      const uint32_t a_base = tmem + lane_addr + col_a + as * 32;
       mbar_wait<2>(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
       tc_fence_after();
       tmem_st8(a_base + 0, ehi);
@@ -538,7 +567,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     asm volatile("cp.async.wait_all;" ::: "memory");
   }
   } else {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsEpi));
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsEpiT));
   if (!(P.exp_flags & 4)) {
     // ===== epilogue: power -> sparse mel -> log(clamp) -> / norm.  4 warps per TMEM lane quarter, one scan chain each =====
     const int q = warp & 3;
@@ -546,7 +575,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const int cb = nb / kChains;                       // bins per chain (multiple of 16)
-    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + kNBMax;
+    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + (uint32_t)nb;
     const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
     const uint32_t bar_done = 1 + q, bar_flushed = 5 + q, bar_clean = 9 + q;   // named barriers of this quarter's four warps
     uint32_t pseq = 0;
@@ -563,7 +592,57 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         const int bin_base = ps * nb + ch * cb;
         mbar_wait<3>(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
         tc_fence_after();
-        for (int r16 = 0; r16 < cb; r16 += 16) {
+        // scan of four consecutive bins whose power is in registers
+        auto scan4 = [&](const float (&pw4)[4], uint32_t advq, int bin0) {
+          const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin0);
+          const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin0 + 2);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (advq & (0x10000u << j)) {            // warp-uniform, rare: two or three filters close
+              const uint32_t cnt = (s_adv2[bin0 >> 4] >> (2 * ((bin0 & 15) + j))) & 3u;
+              park_multi(pa, run_lo, run_hi);
+              run_lo = 0.f; run_hi = 0.f;
+              pa += 4 * cnt;
+              old = ld_s(pa);
+            }
+            if (advq & (1u << j)) {                  // warp-uniform: one filter closes before this bin
+              st_s(pa, old + run_lo);
+              run_lo = run_hi; run_hi = 0.f;
+              pa += 4;
+              old = ld_s(pa);                        // consumed at the next close
+            }
+            const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
+            const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
+            run_lo = fmaf(wl, pw4[j], run_lo);
+            run_hi = fmaf(wh, pw4[j], run_hi);
+          }
+        };
+        auto power_of = [&](uint32_t re, uint32_t im) {
+          const float a = __uint_as_float(re), bq = __uint_as_float(im);
+          float pw = fmaf(a, a, bq * bq);
+          if (kPower1) {
+#if F2_SQRT_APPROX
+            // |X| = sqrt(re^2 + im^2 + eps): the approximate square root (MUFU, <= 1 ulp class error, denormals flushed:
+            // powers below 1e-38 are far under the clamp) instead of the IEEE sequence, 10 instructions per bin shorter
+            pw += P.power_eps;
+            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(pw) : "f"(pw));
+#else
+            pw = sqrtf(pw + P.power_eps);
+#endif
+          }
+          return pw;
+        };
+        auto release_acc = [&]() {                     // my accumulator columns are in registers: hand them back
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) { if (kPair) mbar_arrive_cluster(smem_u32(&bars->acc_empty), 0); else mbar_arrive(smem_u32(&bars->acc_empty)); }
+        };
+        // The last n_hold bins of the chain are pulled into registers as power values in one go, so that the accumulators
+        // go back to the MMA warp BEFORE their scan runs (the scan is issue-bound while all 16 epilogue warps burst); the
+        // first n_stream bins are scanned straight out of TMEM as before.
+        const int n_hold = kDebug ? 0 : (kHold < cb ? kHold : cb);
+        const int n_stream = cb - n_hold;
+        for (int r16 = 0; r16 < n_stream; r16 += 16) {
           const uint32_t advw = s_adv[(bin_base + r16) >> 4];
 #pragma unroll(kQrUnroll)
           for (int qr = 0; qr < 4; ++qr) {             // barely unrolled: the scan stays resident in the instruction cache
@@ -571,11 +650,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             tmem_ld4(t_re + r16 + 4 * qr, re);
             tmem_ld4(t_im + r16 + 4 * qr, im);
             tmem_wait_ld();
-            if (r16 + 16 >= cb && qr == 3) {           // my accumulator columns are in registers: hand them back
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) { if (kPair) mbar_arrive_cluster(smem_u32(&bars->acc_empty), 0); else mbar_arrive(smem_u32(&bars->acc_empty)); }
-            }
+            if (n_hold == 0 && r16 + 16 >= cb && qr == 3) release_acc();
             if (kDebug) {
               const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
               const int t = gi.t0 + lane;
@@ -594,31 +669,38 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
               }
             }
             if (P.exp_flags & 8) continue;
-            const uint32_t advq = advw >> (4 * qr);
-            const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin_base + r16 + 4 * qr);
-            const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin_base + r16 + 4 * qr + 2);
+            float pw4[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (advq & (0x10000u << j)) {            // warp-uniform, rare: two or three filters close
-                const uint32_t cnt = (s_adv2[(bin_base + r16) >> 4] >> (2 * (4 * qr + j))) & 3u;
-                park_multi(pa, run_lo, run_hi);
-                run_lo = 0.f; run_hi = 0.f;
-                pa += 4 * cnt;
-                old = ld_s(pa);
+            for (int j = 0; j < 4; ++j) pw4[j] = power_of(re[j], im[j]);
+            scan4(pw4, advw >> (4 * qr), bin_base + r16 + 4 * qr);
+          }
+        }
+        if (kHold > 0 && n_hold > 0) {
+          float pw[kHold > 0 ? kHold : 4];
+#pragma unroll
+          for (int k8 = 0; k8 < kHold / 8; ++k8) {
+            if (8 * k8 < n_hold) {
+              uint32_t re[8], im[8];
+              tmem_ld8(t_re + n_stream + 8 * k8, re);
+              tmem_ld8(t_im + n_stream + 8 * k8, im);
+              tmem_wait_ld();
+#pragma unroll
+              for (int j = 0; j < 8; ++j) pw[8 * k8 + j] = power_of(re[j], im[j]);
+            }
+          }
+          release_acc();
+          if (!(P.exp_flags & 8)) {
+#pragma unroll
+            for (int k16 = 0; k16 < kHold / 16; ++k16) {
+              if (16 * k16 < n_hold) {
+                const uint32_t advw = s_adv[(bin_base + n_stream + 16 * k16) >> 4];
+#pragma unroll
+                for (int qr = 0; qr < 4; ++qr) {
+                  const float pw4[4] = {pw[16 * k16 + 4 * qr], pw[16 * k16 + 4 * qr + 1], pw[16 * k16 + 4 * qr + 2],
+                                        pw[16 * k16 + 4 * qr + 3]};
+                  scan4(pw4, advw >> (4 * qr), bin_base + n_stream + 16 * k16 + 4 * qr);
+                }
               }
-              if (advq & (1u << j)) {                  // warp-uniform: one filter closes before this bin
-                st_s(pa, old + run_lo);
-                run_lo = run_hi; run_hi = 0.f;
-                pa += 4;
-                old = ld_s(pa);                        // consumed at the next close
-              }
-              const float a = __uint_as_float(re[j]), bq = __uint_as_float(im[j]);
-              float pw = fmaf(a, a, bq * bq);
-              if (kPower1) pw = sqrtf(pw + P.power_eps);
-              const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
-              const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
-              run_lo = fmaf(wl, pw, run_lo);
-              run_hi = fmaf(wh, pw, run_hi);
             }
           }
         }
