@@ -27,11 +27,8 @@
 namespace f2 {
 
 constexpr int kSets = 3;                         // converter sets: set s serves the k-steps with sequence number == s (mod 3)
-constexpr int kAStages2 = 8;                     // most A-operand TMEM stages (32 columns each): the ring takes what the accumulators
-                                                 // leave of the 512 columns -- 4 stages behind 2 x 192 bins (V1), 8 behind 2 x 128 (V2)
-#ifndef F2_ASTAGES_MAX
-#define F2_ASTAGES_MAX 8
-#endif
+constexpr int kAStages2 = 4;                     // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
+                                                 // (8 stages in V2's spare columns: no gain, and the run-time depth cost V1 3 %: profiles/r2g_variants.txt)
 constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
 constexpr int kSlotFloats = 20;                  // 12 forward taps + 8 mirrored taps; 80 B pitch: conflict-free LDS.128
@@ -77,6 +74,7 @@ constexpr int kBStages2 = 4;                      // basis ring depth (single CT
 #define F2_BSTAGES_PAIR 8
 #endif
 constexpr int kBStagesPair = F2_BSTAGES_PAIR;     // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
+constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
 constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
 #ifndef F2_QR_UNROLL
 #define F2_QR_UNROLL 1
@@ -292,9 +290,6 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   if (kPair) cluster_sync_all(); else __syncthreads();       // pair: the peer's barriers must exist before anyone arrives on them
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
-  // TMEM columns: Re [0, nb) | Im [nb, 2 nb) | A ring from 2 nb on (a power-of-two number of 32-column stages)
-  const uint32_t col_a = 2u * (uint32_t)nb;
-  const uint32_t a_stages = (512u - col_a) / 32u >= 8u && F2_ASTAGES_MAX >= 8 ? 8u : 4u, a_shift = a_stages == 8u ? 3u : 2u;
   const int64_t total_groups = P.group_off[P.B];
   const int num_tiles = (int)((total_groups + 3) / 4);
   // a pair walks tiles (2j, 2j+1) in lock step: both CTAs run the same number of iterations, a missing odd tile is empty
@@ -341,7 +336,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t desc_lo0 = (((uint32_t)nbh * 16u) >> 4) << 16;  // LBO = nbh*16 B between the two k-halves
     const uint32_t arr16 = ((uint32_t)nbh * 32u) >> 4;          // one operand array, in 16 B units
     const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
-    const uint32_t d_re = tmem, d_im = tmem + (uint32_t)nb;
+    const uint32_t d_re = tmem, d_im = tmem + kNBMax;
     uint32_t kseq = 0, pseq = 0;
     uint32_t as = 0, ause = 0;                                   // A stage = kseq % kAStages2, its use count
     for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
@@ -362,7 +357,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           }
           tc_fence_after();
           if (elect_one_sync()) {
-            const uint32_t a_base = tmem + col_a + as * 32;
+            const uint32_t a_base = tmem + kColA2 + as * 32;
             const uint32_t lo = desc_lo0 | (sb0 + st * stage16);
             const uint64_t c_hi = ((uint64_t)desc_hi << 32) | lo;
             const uint64_t c_lo = ((uint64_t)desc_hi << 32) | (lo + arr16);
@@ -391,7 +386,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             if (ks == kKS - 1) commit(smem_u32(&bars->acc_full));
           }
           __syncwarp();
-          if (++as == a_stages) { as = 0; ++ause; }
+          if (++as == kAStages2) { as = 0; ++ause; }
         }
       }
     }
@@ -546,8 +541,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       }
       __syncwarp();                                    // every lane has its taps in registers: the stage can be refilled
       issue(stage);
-      const uint32_t as = kseq & (a_stages - 1u), ause = kseq >> a_shift;
-      const uint32_t a_base = tmem + lane_addr + col_a + as * 32;
+      const uint32_t as = kseq % kAStages2, ause = kseq / kAStages2;
+      const uint32_t a_base = tmem + lane_addr + kColA2 + as * 32;
       mbar_wait<2>(smem_u32(&bars->a_empty[as]), (ause & 1) ^ 1, P.status, 402);
       tc_fence_after();
       tmem_st8(a_base + 0, ehi);
@@ -575,7 +570,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const int cb = nb / kChains;                       // bins per chain (multiple of 16)
-    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + (uint32_t)nb;
+    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + kNBMax;
     const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
     const uint32_t bar_done = 1 + q, bar_flushed = 5 + q, bar_clean = 9 + q;   // named barriers of this quarter's four warps
     uint32_t pseq = 0;
