@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _header_symbols():
     names = set()
-    for h in ("ttts_mel.h", "ttts_ingest.h", "ttts_vq.h"):
+    for h in ("ttts_mel.h", "ttts_ingest.h", "ttts_vq.h", "ttts_stft.h"):
         names |= _symbols_of(h)
     names |= _symbols_of("ttts_mel_lab.h", lab=False)        # the measurement hooks both libraries export
     return sorted(names)

@@ -62,6 +62,13 @@ SYMBOLS = {
                                              c_int64, c_int32, c_void_p]),
     "ttts_resample_pcm16_forward": (ctypes.c_int, [c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_int32, c_int64,
                                                    c_void_p, c_int64, c_int32, c_void_p]),
+    # include/ttts_stft.h
+    "ttts_reflect_pad": (ctypes.c_int, [c_void_p, c_int64, c_void_p, c_int32, c_int64, c_int32, c_void_p, c_int64, c_void_p]),
+    "ttts_stft_magnitude": (ctypes.c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, c_float,
+                                           c_int32, c_float, c_void_p, c_void_p]),
+    "ttts_spec_pack": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
+    "ttts_istft_overlap_add": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p, c_void_p,
+                                              c_int64, c_void_p, c_void_p]),
     # include/ttts_vq.h
     "ttts_vq_plan_create": (ctypes.c_int, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
     "ttts_vq_plan_destroy": (None, [c_void_p]),

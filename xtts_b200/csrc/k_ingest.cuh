@@ -395,7 +395,8 @@ extern "C" int ttts_pcm16_to_f32(const int16_t* pcm, int64_t in_stride, int32_t 
 extern "C" int ttts_resample_plan_create(const float* taps, int32_t orig, int32_t new_f, int32_t width,
                                          ttts_resample_plan** out) {
   if (!taps || !out) return fail(TTTS_MEL_EINVAL, "null argument");
-  if (orig < 1 || new_f < 1 || width < 1) return fail(TTTS_MEL_EINVAL, "bad resample geometry %d -> %d, width %d", orig, new_f, width);
+  if (orig < 1 || new_f < 1 || width < 0) return fail   /* width 0: the rows do not overlap (inverse STFT, ttts_stft.h) */
+     (TTTS_MEL_EINVAL, "bad resample geometry %d -> %d, width %d", orig, new_f, width);
   const int kw = 2 * width + orig;
   const int new_pad = (new_f + ingest::kRP - 1) / ingest::kRP * ingest::kRP;
   const int kwp = (kw + 3) / 4 * 4;

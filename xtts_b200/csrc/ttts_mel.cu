@@ -25,6 +25,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
 #include "ttts_mel.h"
 #include "ttts_ingest.h"
+#include "ttts_stft.h"
 
 #include <cuda_runtime.h>
 
@@ -1578,4 +1579,5 @@ extern "C" void ttts_mel_set_experiment(int32_t flags) { g_exp_flags.store(flags
 // ingestion in front of the path (int16 PCM -> float32, sinc resample): include/ttts_ingest.h
 // ------------------------------------------------------------------------------------------
 #include "k_ingest.cuh"
+#include "k_stft.cuh"
 #include "k_vq.cuh"
