@@ -149,16 +149,19 @@ class TorchSTFT(nn.Module):
             con = self._plan(device)
             width = con.width
             d = -(-width // H)                                  # leading rows of the contraction that precede frame 0
-            off0 = (N - W) // 2 - (d * H - width)
-            assert off0 >= 0
+            off0 = (N - W) // 2 - (d * H - width)               # where row 0 of the contraction starts in the padded clip
+            margin = (max(0, -off0) + 3) // 4 * 4               # rows before frame 0 may start left of it: zeros there
             length = (T + d) * H + width                        # samples the contraction may read per clip
             rows = -(-length // H)
-            Lp = (off0 + rows * H + W + 8 + 3) // 4 * 4
-            Lp = max(Lp, (L + 2 * pad + 3) // 4 * 4)
-            xp = torch.empty((B, Lp), dtype=torch.float32, device=device)
+            Lp = (max(off0, 0) + rows * H + W + 8 + margin + 3) // 4 * 4
+            Lp = max(Lp, (L + 2 * pad + margin + 3) // 4 * 4)
+            flat = torch.empty(B * Lp + margin, dtype=torch.float32, device=device)
+            if margin:
+                flat[:margin].zero_()
             _cabi.check(lib.ttts_reflect_pad(x.data_ptr(), int(x.stride(0)) if B > 1 else L, None, B, L, pad,
-                                             xp.data_ptr(), Lp, stream))
-            y = con(xp[:, off0:], length)                       # [B, rows * 2 * bins]: row d + t = frame t, (re, im) pairs
+                                             flat.data_ptr() + 4 * margin, Lp, stream))
+            xv = flat.as_strided((B, Lp - max(off0, 0)), (Lp, 1), margin + off0)
+            y = con(xv, length)                                 # [B, rows * 2 * bins]: row d + t = frame t, (re, im) pairs
             nb = N // 2 + 1
             out = torch.empty((B, nb, T), dtype=torch.float32, device=device)
             power = float(self.power) if self.power is not None else 0.0
