@@ -85,6 +85,9 @@ constexpr int kGroup = 32;                       // frames per group (one conver
 #define F2_HOLD 0
 #endif
 
+#ifndef F2_FAST_LOG
+#define F2_FAST_LOG 1
+#endif
 #ifndef F2_SQRT_APPROX
 #define F2_SQRT_APPROX 1
 #endif
@@ -722,6 +725,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           const GroupInfo gi = locate_group(P, (int64_t)tile * 4 + q, total_groups);
           const int t = gi.t0 + lane;
           float* orow = (gi.valid && t < gi.T && t < P.Tmax) ? P.out + ((int64_t)gi.b * P.Tmax + t) * P.n_mels : nullptr;
+#if F2_FAST_LOG
+          const float log_clamp = logf(P.clamp);
+#endif
           for (int rr0 = 8 * ch; rr0 < ((P.exp_flags & 16) ? 0 : 8 * ch + 8); rr0 += 2) {
             float* rowp[2];
             float v[2][4];
@@ -744,7 +750,13 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
                 for (int i = 0; i < 2; ++i) {
                   // x / norm as reciprocal + one Newton correction: branch-free (the IEEE division's slow-path call
                   // would serialise the chains) and equal to the correctly rounded quotient except in rare last-bit ties
+#if F2_FAST_LOG
+                  // lg2.approx * ln 2 (<= 3 ulp of the result away from 1, 2^-21.4 absolute near it) instead of logf's ~20
+                  // instructions; values at or below the clamp take the exactly rounded constant, so silence stays bit-exact
+                  const float x = v[i][k] > P.clamp ? __logf(v[i][k]) : log_clamp;
+#else
                   const float x = logf(fmaxf(v[i][k], P.clamp));
+#endif
                   if (P.stat_ws && rowp[i]) {
                     // stage (4), fused: per-channel sum / sum of squares of the UN-normalised log-mel in 64-bit fixed point
                     // (steps of 2^-32 for x, 2^-30 for x^2; |x| < 2^5 leaves room for 2^24 frames per launch) -- integer addition is

@@ -553,6 +553,8 @@ __device__ __forceinline__ uint32_t mbar_try_wait_hint(uint32_t bar, uint32_t pa
 }
 template <int kRole>
 __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, int32_t* status, int code) {
+  // (a suspend-time hint on the probe, or a nanosleep between probes of the epilogue's pass-long waits, changes nothing
+  // measurable: profiles/r2a_variants.json, r2l_variants_sleep_fastlog.txt -- the spinning warps do not starve the others)
   const long long t0 = clock64();
   while (!mbar_try_wait_hint(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) mbar_timeout(status, code);
