@@ -14,10 +14,10 @@ ki, vi = h.index("Kernel Name"), h.index("Metric Value")
 agg = collections.OrderedDict()
 for r in data:
     agg.setdefault(r[ki].split("(")[0], []).append(float(r[vi].replace(",", "")) / 1000.0)
-ours = {k: v for k, v in agg.items() if k.startswith("k_") or "k_logmel" in k}
+ours = {k: v for k, v in agg.items() if k in ("k_prep",) or "k_logmel" in k}
 step_us = sum(sum(v) / len(v) for v in ours.values())
 with open(os.path.join(out_dir, f"{tag}_launch_list_summary.md"), "w") as f:
-    f.write(f"# ncu launch list ({tag}): `ncu --metrics gpu__time_duration.sum --clock-control none -c 120 python bench.py --steps 20 --warmup 3`\n\n")
+    f.write(f"# ncu launch list ({tag}): `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-sweep`\n\n")
     f.write("Per-launch times under ncu are cold-cache and serialised: compare SHARES, not absolutes.\n\n")
     f.write("| kernel | launches | mean us | min us | share of our kernels per step |\n|---|---|---|---|---|\n")
     for k, v in agg.items():
@@ -46,7 +46,9 @@ wr = [f(v) for v in met["dram__bytes_write.sum"]["per_launch"]]
 scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1}
 rb = sum(rd) / len(rd) * scale[met["dram__bytes_read.sum"]["unit"]]
 wb = sum(wr) / len(wr) * scale[met["dram__bytes_write.sum"]["unit"]]
-summary = {"kernel": "k_logmel2<false,false>", "workload": "64x10s (55168 frames) per launch", "source": os.path.basename(rep),
+kname = next((r[hh.index("Kernel Name")] for r in rr[2:] if len(r) > 5), "k_logmel2") if "Kernel Name" in hh else "k_logmel2"
+commit = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True, cwd=ROOT).stdout.strip()
+summary = {"kernel": kname, "workload": "64x10s (55168 frames) per launch", "source": os.path.basename(rep), "commit": commit,
            "dram_bytes_per_launch": rb + wb, "dram_read_bytes": rb, "dram_write_bytes": wb,
            "algorithmic_bytes_per_launch": 55168 * 1344, "metrics": met}
 json.dump(summary, open(os.path.join(out_dir, "k_logmel_ncu_metrics.json"), "w"), indent=1)
