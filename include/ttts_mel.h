@@ -85,6 +85,12 @@ int32_t ttts_mel_live_bins(const ttts_mel_plan* plan);  /* bins with a non-zero 
 /* Bytes of device workspace ttts_mel_forward needs for a batch of B clips of at most Lmax samples. */
 size_t ttts_mel_workspace_bytes(const ttts_mel_plan* plan, int32_t B, int64_t Lmax);
 
+/* The same for one particular input: when its rows are 16-byte addressable (base and row_stride * 4 multiples of 16)
+ * the kernel reads the waveform in place and the padded copy -- as large as the batch -- is not part of the workspace.
+ * ttts_mel_forward accepts either size for such an input. */
+size_t ttts_mel_workspace_bytes_for(const ttts_mel_plan* plan, int32_t B, int64_t Lmax, const float* wav_dev,
+                                    int64_t row_stride);
+
 /* Replaces TorchMelSpectrogram.forward / MelSpectrogramFeatures.forward
  * (ttts/utils/utils.py:509-522, ttts/vocoder/feature_extractors.py:93-99) on a batch.
  *   wav_dev      [B, row_stride] fp32, clip b occupies wav_dev[b*row_stride .. +length_b)

@@ -41,6 +41,7 @@ SYMBOLS = {
     "ttts_mel_plan_destroy": (None, [c_void_p]),
     "ttts_mel_frames": (c_int64, [c_void_p, c_int64]),
     "ttts_mel_workspace_bytes": (c_size_t, [c_void_p, c_int32, c_int64]),
+    "ttts_mel_workspace_bytes_for": (c_size_t, [c_void_p, c_int32, c_int64, c_void_p, c_int64]),
     "ttts_mel_forward": (ctypes.c_int, _FWD_ARGS),
     "ttts_mel_forward_stats": (ctypes.c_int, _FWD_ARGS + [c_void_p]),
     "ttts_mel_config_size": (c_size_t, []),

@@ -480,7 +480,9 @@ struct Workspace {
   size_t bytes;
 };
 
-Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
+// `direct`: the fused kernel reads the caller's waveform in place (16-byte addressable rows), so the fully padded copy
+// `xp` -- as large as the batch itself -- is not needed and not reserved.
+Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax, bool direct = false) {
   Workspace w{};
   const int64_t T = 1 + (Lmax + 2 * p->cfg.pad - kNfft) / kHop;
   w.Lp = (int64_t)align_up((size_t)(kHop * (T > 0 ? T - 1 : 0) + kNfft + 64), 64);
@@ -492,7 +494,7 @@ Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
   w.group_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.n_frames = (int32_t*)(b + off); off += align_up((size_t)B * 4, 256);
   w.edge = (float*)(b + off); off += align_up((size_t)B * kEdgeClip * 4, 256);
-  w.xp = (float*)(b + off); off += align_up((size_t)B * (size_t)w.Lp * 4, 256);
+  w.xp = (float*)(b + off); off += direct ? 0 : align_up((size_t)B * (size_t)w.Lp * 4, 256);
   w.bytes = off;
   return w;
 }
@@ -502,6 +504,16 @@ Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax) {
 extern "C" size_t ttts_mel_workspace_bytes(const ttts_mel_plan* p, int32_t B, int64_t Lmax) {
   if (!p || B <= 0 || Lmax <= 0) return 0;
   return carve(p, nullptr, B, Lmax).bytes;
+}
+
+static bool reads_in_place(const void* wav, int64_t row_stride, int32_t B) {
+  return (row_stride % 4 == 0) && (((uintptr_t)wav & 15) == 0) && (int64_t)B * row_stride < ((int64_t)1 << 31);
+}
+
+extern "C" size_t ttts_mel_workspace_bytes_for(const ttts_mel_plan* p, int32_t B, int64_t Lmax, const float* wav,
+                                               int64_t row_stride) {
+  if (!p || B <= 0 || Lmax <= 0) return 0;
+  return carve(p, nullptr, B, Lmax, reads_in_place(wav, row_stride, B)).bytes;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1351,7 +1363,8 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   CUDA_TRY(cudaGetDevice(&cur_dev));
   if (cur_dev != p->device) return fail(TTTS_MEL_EINVAL, "plan lives on device %d, the current device is %d", p->device, cur_dev);
   if (ttts_mel_frames(p, Lmax) < 0) return TTTS_MEL_EINVAL;
-  Workspace w = carve(p, ws_ptr, B, Lmax);
+  const bool in_place = impl == Impl::Tcgen05 && reads_in_place(wav, row_stride, B);
+  Workspace w = carve(p, ws_ptr, B, Lmax, in_place);
   if (ws_bytes < w.bytes) return fail(TTTS_MEL_ENOMEM, "workspace %zu < %zu bytes", ws_bytes, w.bytes);
   if ((int64_t)B * w.Lp >= (int64_t)1 << 31) return fail(TTTS_MEL_EINVAL, "batch too large for 32-bit row offsets: split it");
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -1360,7 +1373,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   // k_logmel reads the caller's waveform directly when it is 16 B-addressable; only the frames that touch
   // the reflect padding go through a small edge buffer.  Otherwise (and for k_simt) the clips are padded
   // into the workspace first.
-  const bool direct = impl == Impl::Tcgen05 && vec_ok && (int64_t)B * row_stride < ((int64_t)1 << 31);
+  const bool direct = in_place;
   k_prep<<<kPrepSplit * B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
                                      p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status,
                                      stat_acc ? w.stat : nullptr);

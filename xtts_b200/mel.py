@@ -133,14 +133,16 @@ class MelPlan:
             if len_dev.numel() != B:
                 raise ValueError("lengths must have one entry per clip")
         with torch.cuda.device(self.device):
-            ws_bytes = int(lib.ttts_mel_workspace_bytes(self._h, B, Lmax))
+            row_stride = int(wav.stride(0)) if B > 1 else Lmax      # a size-1 batch dimension may carry any stride
+            if impl == "tcgen05":       # in-place inputs do not need the padded copy (half the transient memory at 32 x 120 s)
+                ws_bytes = int(lib.ttts_mel_workspace_bytes_for(self._h, B, Lmax, wav.data_ptr(), row_stride))
+            else:
+                ws_bytes = int(lib.ttts_mel_workspace_bytes(self._h, B, Lmax))
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
             out = torch.empty((B, T, self.n_mels), dtype=torch.float32, device=self.device)
             n_frames = torch.empty((B,), dtype=torch.int32, device=self.device)
             mask = torch.empty((B, T), dtype=torch.uint8, device=self.device) if want_mask else None
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            # a size-1 batch dimension may carry any stride (torch treats it as contiguous): the row stride is moot
-            row_stride = int(wav.stride(0)) if B > 1 else Lmax
             args = [self._h, wav.data_ptr(), row_stride, len_dev.data_ptr() if len_dev is not None else None,
                     B, Lmax, T, out.data_ptr(), n_frames.data_ptr(), mask.data_ptr() if mask is not None else None,
                     ws.data_ptr(), ws_bytes, stream]

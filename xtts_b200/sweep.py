@@ -322,7 +322,10 @@ def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, 
     resample, clip: utils.py:32-47) on the device.  ``max_len`` is in samples at the TARGET rate (what the buckets
     are built from); the batch is padded to the longest source clip."""
     from .ingest import load_audio_pcm16
-    stage = {"buf": None, "free": None}
+    # two pinned staging buffers used alternately: the host fills one while the other's H2D copy and the kernels of the
+    # previous batch are still in flight (everything after the fill is asynchronous on the current stream)
+    stage = [{"buf": None, "free": None}, {"buf": None, "free": None}]
+    turn = [0]
 
     def fetch(indices, max_len):
         import numpy as np
@@ -331,13 +334,15 @@ def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, 
         F = max(int(c.shape[0]) for c in clips)
         C = int(clips[0].shape[1])
         need = len(clips) * F * C
-        if stage["buf"] is None or stage["buf"].numel() < need:      # one pinned staging buffer, grown on demand
-            stage["buf"] = torch.empty(max(need, 2 * (stage["buf"].numel() if stage["buf"] is not None else 0)),
-                                       dtype=torch.int16, pin_memory=pinned)
-            stage["free"] = None
-        if stage["free"] is not None:
-            stage["free"].synchronize()                              # the previous batch's H2D copy has left the buffer
-        host = stage["buf"][:need].view(len(clips), F, C)
+        st = stage[turn[0]]
+        turn[0] ^= 1
+        if st["buf"] is None or st["buf"].numel() < need:            # grown on demand
+            st["buf"] = torch.empty(max(need, 2 * (st["buf"].numel() if st["buf"] is not None else 0)),
+                                    dtype=torch.int16, pin_memory=pinned)
+            st["free"] = None
+        if st["free"] is not None:
+            st["free"].synchronize()                                 # the copy issued two batches ago has left this buffer
+        host = st["buf"][:need].view(len(clips), F, C)
         host.zero_()
         for b, c in enumerate(clips):
             if int(c.shape[1]) != C:
@@ -346,8 +351,8 @@ def pcm16_fetch(read_pcm: Callable, source_rate: int, target_rate: int, device, 
         frames = torch.tensor([int(c.shape[0]) for c in clips], dtype=torch.int64)
         dev_pcm = host.to(device, non_blocking=True)
         if dev_pcm.is_cuda:
-            stage["free"] = torch.cuda.Event()
-            stage["free"].record(torch.cuda.current_stream(dev_pcm.device))
+            st["free"] = torch.cuda.Event()
+            st["free"].record(torch.cuda.current_stream(dev_pcm.device))
         wav, lens = load_audio_pcm16(dev_pcm, source_rate, target_rate, frames, kernel_dtype=kernel_dtype)
         return wav, lens
 
