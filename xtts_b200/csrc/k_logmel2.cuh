@@ -26,7 +26,13 @@
 
 namespace f2 {
 
-constexpr int kSets = 3;                         // converter sets: set s serves the k-steps with sequence number == s (mod 3)
+#ifndef F2_SETS
+#define F2_SETS 3
+#endif
+#ifndef F2_CHAINS
+#define F2_CHAINS 4
+#endif
+constexpr int kSets = F2_SETS;                   // converter sets: set s serves the k-steps with sequence number == s (mod kSets)
 constexpr int kAStages2 = 4;                     // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
                                                  // (8 stages in V2's spare columns: no gain, and the run-time depth cost V1 3 %: profiles/r2g_variants.txt)
 constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
@@ -42,7 +48,7 @@ constexpr int kPieceIters = (kPieces + 31) / 32;
 constexpr int kConvWarps2 = 4 * kSets;
 constexpr int kWarpConv02 = 4;
 constexpr int kWarpEpi02 = kWarpConv02 + kConvWarps2;
-constexpr int kEpiWarps = 4 * 4;                   // 4 lane quarters x kChains scan chains
+constexpr int kEpiWarps = 4 * F2_CHAINS;           // 4 lane quarters x kChains scan chains
 constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
 // registers per thread by role (setmaxnreg, per warpgroup): 128*40 + 384*96 + 512*40 = 62464 <= 65536; launch value 64
 #ifndef F2_REGS_MISC
@@ -55,7 +61,7 @@ constexpr int kThreads2 = (kWarpEpi02 + kEpiWarps) * 32;
 #define F2_REGS_EPI 40
 #endif
 constexpr int kRegsMisc = F2_REGS_MISC, kRegsConv = F2_REGS_CONV, kRegsEpi = F2_REGS_EPI;
-static_assert(128 * kRegsMisc + 384 * kRegsConv + 512 * kRegsEpi <= 65536, "register budgets exceed the file");
+static_assert(128 * kRegsMisc + 128 * kSets * kRegsConv + 128 * F2_CHAINS * kRegsEpi <= 65536, "register budgets exceed the file");
 // magnitude (power 1) instantiations: the epilogue holds its chain's last 32 bins as power values in registers and hands
 // the accumulators back before scanning them (measured, profiles/r2e_variants_hold_sqrt.txt: V2 -3 %, V1 +1.6 %: V1 keeps
 // the streaming scan and round 1's budgets)
@@ -68,14 +74,15 @@ static_assert(128 * kRegsMisc + 384 * kRegsConv + 512 * kRegsEpi <= 65536, "regi
 #ifndef F2_HOLD_P1
 #define F2_HOLD_P1 32
 #endif
-static_assert(128 * kRegsMisc + 384 * F2_REGS_CONV_P1 + 512 * F2_REGS_EPI_P1 <= 65536, "register budgets exceed the file");
+static_assert(128 * kRegsMisc + 128 * kSets * F2_REGS_CONV_P1 + 128 * F2_CHAINS * F2_REGS_EPI_P1 <= 65536, "register budgets exceed the file");
 constexpr int kBStages2 = 4;                      // basis ring depth (single CTA: 4 x 24 KB)
 #ifndef F2_BSTAGES_PAIR
 #define F2_BSTAGES_PAIR 8
 #endif
 constexpr int kBStagesPair = F2_BSTAGES_PAIR;     // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
 constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
-constexpr int kChains = 4;                       // mel-scan chains per pass, one epilogue warp each (per lane quarter)
+constexpr int kChains = F2_CHAINS;               // mel-scan chains per pass, one epilogue warp each (per lane quarter)
+static_assert(kThreads2 == 1024 && kAStages2 % 1 == 0, "4 misc + 4 kSets + 4 kChains warps must be 32");
 #ifndef F2_QR_UNROLL
 #define F2_QR_UNROLL 1
 #endif
@@ -707,9 +714,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         fl[0] = run_lo;
         fl[kTileM] = run_hi;
         if (ch != 0) {
-          asm volatile("bar.arrive %0, 128;" ::"r"(bar_done) : "memory");
+          asm volatile("bar.arrive %0, %1;" ::"r"(bar_done), "n"(32 * kChains) : "memory");
         } else {
-          asm volatile("bar.sync %0, 128;" ::"r"(bar_done) : "memory");
+          asm volatile("bar.sync %0, %1;" ::"r"(bar_done), "n"(32 * kChains) : "memory");
 #pragma unroll
           for (int c = 0; c < kChains; ++c) {
             const float* f = s_fl + ((pseq & 1) * kChains + c) * 2 * kTileM + r;
@@ -717,7 +724,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           }
         }
         // nobody starts the next scan (or the log pass) before the open pairs are in the park rows
-        asm volatile("bar.sync %0, 128;" ::"r"(bar_flushed) : "memory");
+        asm volatile("bar.sync %0, %1;" ::"r"(bar_flushed), "n"(32 * kChains) : "memory");
         if (ps == P.passes - 1) {
           // raw mel sums -> log(max(., clamp)) / norm.  Each of the quarter's four warps takes 8 of its 32 rows: coalesced
           // output rows, 2 rows x up to 4 columns per lane in flight (independent logf / division chains); the park rows
@@ -728,17 +735,21 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 #if F2_FAST_LOG
           const float log_clamp = logf(P.clamp);
 #endif
-          for (int rr0 = 8 * ch; rr0 < ((P.exp_flags & 16) ? 0 : 8 * ch + 8); rr0 += 2) {
+          // the quarter's 32 rows are split over its kChains warps (8 each for four chains; 10 / 11 / 11 for three)
+          const int row_lo = (32 * ch) / kChains, row_hi = (32 * (ch + 1)) / kChains;
+          for (int rr0 = row_lo; rr0 < ((P.exp_flags & 16) ? 0 : row_hi); rr0 += 2) {
             float* rowp[2];
             float v[2][4];
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-              rowp[i] = reinterpret_cast<float*>((uintptr_t)__shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, rr0 + i));
+              const bool mine = (32 % kChains == 0) || rr0 + i < row_hi;      // an odd share ends on a single row
+              rowp[i] = reinterpret_cast<float*>((uintptr_t)__shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)orow, (rr0 + i) & 31));
+              if (!mine) rowp[i] = nullptr;
               float* parked = s_park + (q * 32 + rr0 + i) * park_pitch + lane;
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 v[i][k] = 1.f;
-                if (lane + 32 * k < P.n_mels) { v[i][k] = parked[32 * k]; parked[32 * k] = 0.f; }
+                if (mine && lane + 32 * k < P.n_mels) { v[i][k] = parked[32 * k]; parked[32 * k] = 0.f; }
               }
             }
 #pragma unroll
@@ -780,7 +791,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
               for (int k = 0; k < 4; ++k)
                 if (rowp[i] && lane + 32 * k < P.n_mels) rowp[i][lane + 32 * k] = v[i][k];
           }
-          asm volatile("bar.sync %0, 128;" ::"r"(bar_clean) : "memory");   // all 32 park rows of the quarter are zero again
+          asm volatile("bar.sync %0, %1;" ::"r"(bar_clean), "n"(32 * kChains) : "memory");   // all 32 park rows of the quarter are zero again
         }
       }
     }

@@ -72,7 +72,10 @@ constexpr int kAStages = 4;
 constexpr int kThreads = 512;
 constexpr int kMaxMels = 128;
 constexpr long long kTimeoutCycles = 4000000000LL;
-constexpr int f2_kChains = 4;          // mel-scan chains per epilogue thread of k_logmel2 (== f2::kChains)
+#ifndef F2_CHAINS
+#define F2_CHAINS 4
+#endif
+constexpr int f2_kChains = F2_CHAINS;  // mel-scan chains per epilogue thread of k_logmel2 (== f2::kChains)
 
 // warp roles of k_logmel
 constexpr int kWarpTma = 0, kWarpMma = 1, kWarpTmem = 2;   // warp 3 is spare
@@ -299,7 +302,8 @@ extern "C" int ttts_mel_plan_create(const ttts_mel_config* cfg, const float* fb,
   for (int q = 0; q < 2; ++q) n_par[q] = p->first_k[q] <= kmax ? (kmax - p->first_k[q]) / 2 + 1 : 0;
   const int n_par_max = n_par[0] > n_par[1] ? n_par[0] : n_par[1];
   p->sp = (n_par_max + kNBMax - 1) / kNBMax;
-  p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 64);   // 4 scan chains of whole 16-bin blocks
+  p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 16 * f2_kChains);   // scan chains of whole 16-bin blocks
+  if (p->nb2 > kNBMax) { p->sp += 1; p->nb2 = (int)align_up((size_t)((n_par_max + p->sp - 1) / p->sp), 16 * f2_kChains); }
   p->nbt2 = 2 * p->sp * p->nb2;
 #ifdef TTTS_MEL_LAB
   if (const char* e2 = lab_env("TTTS_MEL_ALGO")) p->algo = atoi(e2) == 1 ? 1 : 2;
