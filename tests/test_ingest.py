@@ -401,31 +401,3 @@ def test_gpu_plans_of_different_sizes_coexist():
     tiny(x)
     assert torch.equal(big(x), y0)
 
-
-@gpu
-def test_gpu_persistent_decimator_is_bit_identical_to_the_tiled_one(monkeypatch):
-    """k_decimate2 (persistent, cp.async ring; the default for 16-byte addressable 2:1 inputs) against k_decimate (lab
-    knob TTTS_DECIMATE_V1): same arithmetic order -> identical bits, float32 and fused stereo int16, dense and ragged,
-    several tiles per clip and more tiles than CTAs."""
-    from xtts_b200 import Resampler, _cabi
-    new = Resampler(44100, 22050)
-    _cabi.select_lab(True)
-    monkeypatch.setenv("TTTS_DECIMATE_V1", "1")
-    try:
-        old = Resampler(44100, 22050)
-        x = torch.rand((7, 100004), device="cuda") * 2 - 1
-        lens = torch.tensor([100004, 1, 2, 33333, 4099, 99999, 50000])
-        pcm = torch.randint(-32768, 32767, (7, 100004, 2), dtype=torch.int16, device="cuda")
-        big = torch.rand((300, 441000 // 10 * 4), device="cuda") * 2 - 1          # 300 clips x 44 tiles: > 5 x 148 CTAs
-        ya, la = new(x, lens, clip=True)
-        yb, lb = old(x, lens, clip=True)
-        assert torch.equal(la, lb) and torch.equal(ya, yb)
-        assert torch.equal(new(x), old(x))
-        pa, qa = new.from_pcm16(pcm, lens, clip=True)
-        pb, qb = old.from_pcm16(pcm, lens, clip=True)
-        assert torch.equal(qa, qb) and torch.equal(pa, pb)
-        assert torch.equal(new.from_pcm16(pcm), old.from_pcm16(pcm))
-        assert torch.equal(new(big), old(big))
-    finally:
-        monkeypatch.delenv("TTTS_DECIMATE_V1")
-        _cabi.select_lab(False)

@@ -103,6 +103,9 @@ __device__ __forceinline__ float4 quad_to_float(const int16_t*, int4 w, int chan
                      pcm16_to_float((uint32_t)w.z), pcm16_to_float((uint32_t)w.w));
 }
 
+// (Round 2, tried and dropped -- profiles/r2p_decimator_variants.txt, 64 x 10 s 44.1 -> 22.05 kHz: this kernel 46 us fp32 /
+//  53 us fused stereo PCM = 3.7 / 3.2 TB/s; a persistent CTA with a two-deep cp.async ring 51 / 58 us (fewer resident warps
+//  overlap less than eight independent CTAs per SM do); packed fma.rn.f32x2 taps 52 / 66 us (FFMA2 issues at half rate).)
 // new == 1: out[j] = sum_k xpad[j * ORIG + k] * taps[k].  One CTA = 2048 consecutive outputs of one clip: the
 // segment is staged once in shared memory (16-byte loads and stores: it starts at the multiple of 4 at or below
 // the first sample the tile needs, kOff samples early), each thread pulls the samples its 8 outputs share into
@@ -189,116 +192,6 @@ __global__ void __launch_bounds__(kThreads) k_decimate(const TIn* __restrict__ x
     for (int r = 0; r < kDecR; ++r)
       if (j + r < out_cols) dst[j + r] = acc[r];
   }
-}
-
-// ---------------------------------------------------------------------------------------------- k_decimate2
-// The same FIR, same arithmetic order (results bit-identical to k_decimate), as a persistent kernel: every CTA walks
-// tiles of 2048 outputs and stages tile i + 1 with 16-byte cp.async into the other half of a two-deep shared-memory ring
-// while it computes tile i -- k_decimate's CTAs alternate "all loads" / barrier / "all FMAs" and reach 0.5 of the HBM
-// copy bandwidth with the staging loads as their long-scoreboard stall (profiles/r1d_ingest_ncu.md).  float32 input, or
-// interleaved stereo int16 (one 32-bit word per frame: the raw words are staged and channel 0 is converted as the window
-// is pulled into registers).  Needs 16-byte addressable rows; anything else stays with k_decimate.
-__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, uint32_t bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ float word_to_float(const float*, uint32_t w) { return __uint_as_float(w); }
-__device__ __forceinline__ float word_to_float(const int16_t*, uint32_t w) { return pcm16_to_float(w); }
-
-template <int ORIG, int KW, typename TIn>
-__global__ void __launch_bounds__(kThreads) k_decimate2(const TIn* __restrict__ x, long long row_stride,
-                                                        const long long* __restrict__ lengths, long long L,
-                                                        const TapsParam taps, float* __restrict__ out,
-                                                        long long out_stride, long long out_cols, int clip,
-                                                        int tiles_per_clip, long long total_tiles) {
-  constexpr int kWidth = (KW - ORIG) / 2;
-  constexpr int kOff = (4 - (kWidth & 3)) & 3;
-  constexpr int kWin = kOff + (kDecR - 1) * ORIG + KW;
-  constexpr int kWinQ = (kWin + 3) / 4;
-  constexpr int kSeg = (kThreads - 1) * kDecR * ORIG + kWinQ * 4;
-  constexpr int kQuads = kSeg / 4, kIt = (kQuads + kThreads - 1) / kThreads;
-  constexpr int kBuf = kSeg + (kSeg >> 4) * 4 + 4;                  // words per ring stage (dec_pad layout)
-  __shared__ __align__(16) uint32_t xs[2][kBuf];
-
-  auto stage = [&](long long tile, int buf) {
-    if (tile >= total_tiles) return;
-    const int b = (int)(tile / tiles_per_clip);
-    const long long j0 = (tile - (long long)b * tiles_per_clip) * kDecTile;
-    const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
-    if (j0 >= (len + ORIG - 1) / ORIG) return;                       // nothing of the clip in this tile: zeros are stored
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(x + (long long)b * row_stride);
-    const long long s0 = j0 * ORIG - kWidth - kOff;                  // multiple of 4 (negative for a clip's first tile)
-    const uint32_t base = (uint32_t)__cvta_generic_to_shared(&xs[buf][0]);
-#pragma unroll
-    for (int it = 0; it < kIt; ++it) {
-      const int q = threadIdx.x + it * kThreads;
-      if (q >= kQuads) break;
-      const long long s = s0 + 4 * q;
-      const uint32_t dst = base + 4u * (uint32_t)dec_pad(4 * q);
-      if (s >= 0) {                                                  // whole chunk, a prefix of it, or nothing (zero fill)
-        const long long left = len - s;
-        const uint32_t bytes = left >= 4 ? 16u : (left > 0 ? (uint32_t)left * 4u : 0u);
-        cp_async16_zfill(dst, bytes ? (const void*)(src + s) : (const void*)src, bytes);
-      } else {                                                       // straddles the clip's start: scalar
-        uint32_t w[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) w[e] = (s + e >= 0 && s + e < len) ? __ldg(src + s + e) : 0u;
-        *reinterpret_cast<uint4*>(&xs[buf][dec_pad(4 * q)]) = make_uint4(w[0], w[1], w[2], w[3]);
-      }
-    }
-  };
-
-  long long tile = blockIdx.x;
-  stage(tile, 0);
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  for (int i = 0; tile < total_tiles; tile += gridDim.x, ++i) {
-    const int buf = i & 1;
-    stage(tile + gridDim.x, buf ^ 1);                                // the other stage was released by the barrier below
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    __syncthreads();
-    const int b = (int)(tile / tiles_per_clip);
-    const long long j0 = (tile - (long long)b * tiles_per_clip) * kDecTile;
-    const long long len = lengths ? min(max(lengths[b], 0LL), L) : L;
-    const long long olen = (len + ORIG - 1) / ORIG;
-    float* dst = out + (long long)b * out_stride;
-    const long long j = j0 + (long long)threadIdx.x * kDecR;
-    float acc[kDecR];
-#pragma unroll
-    for (int r = 0; r < kDecR; ++r) acc[r] = 0.f;
-    if (j0 < olen) {
-      float w[kWinQ * 4];
-      const int start = threadIdx.x * (kDecR * ORIG);
-#pragma unroll
-      for (int c = 0; c < kWinQ; ++c) {
-        const uint4 v = *reinterpret_cast<const uint4*>(&xs[buf][dec_pad(start + 4 * c)]);
-        w[4 * c] = word_to_float(x, v.x); w[4 * c + 1] = word_to_float(x, v.y);
-        w[4 * c + 2] = word_to_float(x, v.z); w[4 * c + 3] = word_to_float(x, v.w);
-      }
-      // (a zero-filled word converts to exactly 0.0f in both input types)
-#pragma unroll
-      for (int k = 0; k < KW; ++k) {
-        const float t = taps.t[k];
-#pragma unroll
-        for (int r = 0; r < kDecR; ++r) acc[r] = fmaf(w[kOff + r * ORIG + k], t, acc[r]);
-      }
-#pragma unroll
-      for (int r = 0; r < kDecR; ++r) {
-        float v = (j + r < olen) ? acc[r] : 0.f;
-        if (clip) v = fminf(fmaxf(v, -1.f), 1.f);
-        acc[r] = v;
-      }
-    }
-    if (j + kDecR <= out_cols) {
-      reinterpret_cast<float4*>(dst + j)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      reinterpret_cast<float4*>(dst + j)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-    } else {
-#pragma unroll
-      for (int r = 0; r < kDecR; ++r)
-        if (j + r < out_cols) dst[j + r] = acc[r];
-    }
-    __syncthreads();                                                 // everyone has read this stage: it may be refilled
-  }
-  asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 // ---------------------------------------------------------------------------------------------- k_resample
@@ -653,22 +546,6 @@ int resample_launch(const ttts_resample_plan* p, const TIn* x, int64_t row_strid
     // all staging loads before the first conversion pays for fp32 and mono PCM; for stereo PCM (two 16-byte loads'
     // worth of raw words per quad of samples) the registers it takes cost more occupancy than the overlap wins
     const bool hoist = sizeof(TIn) == 4 || channels == 1;
-    // persistent, double-buffered variant for 16-byte addressable float32 / stereo int16 rows (k_decimate2)
-    const bool words_ok = sizeof(TIn) == 4 ? (row_stride % 4 == 0) : (channels == 2 && row_stride % 8 == 0);
-    // (2:1 only: two stages of the 3:1 / 4:1 segments exceed the 48 KB of static shared memory)
-    if (p->orig == 2 && words_ok && (uintptr_t)x % 16 == 0 && out_stride % 4 == 0 && (uintptr_t)out % 16 == 0 &&
-        !lab_env("TTTS_DECIMATE_V1")) {
-      const long long total = gx * (long long)B;
-      int sms = 148;
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device);
-      const unsigned g2 = (unsigned)std::min<long long>(total, (long long)sms * 5);     // 42 KB of shared memory each: 5 per SM
-#define TTTS_DEC2(O, K) ingest::k_decimate2<O, K, TIn><<<g2, ingest::kThreads, 0, st>>>( \
-          x, row_stride, len, L, p->taps1, out, out_stride, out_cols, clip, (int)gx, total)
-      TTTS_DEC2(2, 28);
-#undef TTTS_DEC2
-      CUDA_TRY(cudaGetLastError());
-      return TTTS_MEL_OK;
-    }
 #define TTTS_DEC(O, K) do { \
       if (hoist) ingest::k_decimate<O, K, TIn, true><<<grid, ingest::kThreads, 0, st>>>( \
           x, row_stride, channels, len, L, p->taps1, out, out_stride, out_cols, clip, vec); \
