@@ -124,14 +124,6 @@ struct Params {
   int32_t* status;
   unsigned long long* stat_ws;  // fused statistics: [2 * kMaxMels] fixed-point sums of this launch + [1] CTA ticket (zeroed by k_prep), or null
   double* stat_acc;           // [2 * n_mels + 1] fp64, += at the end of the launch by the last CTA
-  int stat_count;             // this launch adds the batch's frame count to stat_acc[2 n_mels] (one launch per forward does)
-  // tail split (kSplit instantiation, dense batches): the tile pairs a last, part-filled round would hold are dealt at
-  // (tile pair, pass) granularity -- CTA pair u takes pass u % passes of tile pair split_tile0 / 2 + u / passes -- and the
-  // main launch stops at tile_limit
-  int tile_limit;             // main launch: first tile it does NOT process (INT_MAX: all)
-  int split_tile0;            // tail launch: first tile of the split range
-  float* split_part;          // [split tiles][passes][128][n_mels] raw mel sums of one pass
-  int* split_cnt;             // [split tiles] arrival tickets (zeroed by k_prep)
   float* dbg_reim;            // optional [total_frames][2*dbg_nbt], bins dbg_kmin..
   int dbg_nbt, dbg_kmin, kmax;
   int first_k[2];             // first live bin of each parity
@@ -248,7 +240,7 @@ __device__ __forceinline__ void tc_commit2(uint32_t bar) {
 // every basis stage (96 of the 192 bins) -- the tensor cores of both SMs read both halves.  Per SM that halves the
 // basis L2 -> smem traffic, the smem space of the basis ring and the B-operand smem reads.  CTA 0 issues the MMAs; the
 // peer's converters / epilogue arrive on CTA 0's barriers, tcgen05.commit multicasts to both CTAs' barriers.
-template <bool kPower1, bool kDebug, bool kPair, bool kSplit = false>
+template <bool kPower1, bool kDebug, bool kPair>
 __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P) {
   using namespace f2;
   constexpr int kBS = kPair ? kBStagesPair : kBStages2;    // basis ring depth
@@ -309,15 +301,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   tc_fence_after();
   const uint32_t tmem = *s_tmem;
   const int64_t total_groups = P.group_off[P.B];
-  const int all_tiles = (int)((total_groups + 3) / 4);
-  const int num_tiles = kSplit ? all_tiles : (all_tiles < P.tile_limit ? all_tiles : P.tile_limit);
+  const int num_tiles = (int)((total_groups + 3) / 4);
   // a pair walks tiles (2j, 2j+1) in lock step: both CTAs run the same number of iterations, a missing odd tile is empty
   auto tile_live = [&](int tile) { return (kPair ? (tile & ~1) : tile) < num_tiles; };
-  // this CTA's work: tiles tile0, tile0 + tstep, ... and passes [ps0, ps1) of each.  Tail split: ONE pass of ONE tile
-  const int tile0 = kSplit ? P.split_tile0 + 2 * (int)((blockIdx.x >> 1) / (unsigned)P.passes) + (int)cta_rank : (int)blockIdx.x;
-  const int tstep = kSplit ? (1 << 28) : (int)gridDim.x;
-  const int ps0 = kSplit ? (int)((blockIdx.x >> 1) % (unsigned)P.passes) : 0;
-  const int ps1 = kSplit ? ps0 + 1 : P.passes;
 
   const int wgroup = warp >> 2;                        // setmaxnreg works on warpgroups: misc | converters | epilogue
   if (wgroup == 0) {
@@ -326,8 +312,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     // ===== basis producer: one bulk copy per k-step stage =====
     if (lane == 0 && !(P.exp_flags & 2)) {
       uint32_t seq = 0;
-      for (int tile = tile0; tile_live(tile); tile += tstep)
-        for (int ps = ps0; ps < ps1; ++ps)
+      for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
+        for (int ps = 0; ps < P.passes; ++ps)
           for (int ks = 0; ks < kKS; ++ks, ++seq) {
             const uint32_t st = seq % kBS, use = seq / kBS;
             mbar_wait<1>(smem_u32(&bars->b_empty[st]), (use & 1) ^ 1, P.status, 101);
@@ -344,8 +330,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       // peer CTA: no MMAs to issue; tell the leader when my half of each basis stage has landed
       if (lane == 0 && !(P.exp_flags & 2)) {
         uint32_t seq = 0;
-        for (int tile = tile0; tile_live(tile); tile += tstep)
-          for (int ps = ps0; ps < ps1; ++ps)
+        for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
+          for (int ps = 0; ps < P.passes; ++ps)
             for (int ks = 0; ks < kKS; ++ks, ++seq) {
               const uint32_t st = seq % kBS, use = seq / kBS;
               mbar_wait<1>(smem_u32(&bars->b_full[st]), use & 1, P.status, 204);
@@ -363,8 +349,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t d_re = tmem, d_im = tmem + kNBMax;
     uint32_t kseq = 0, pseq = 0;
     uint32_t as = 0, ause = 0;                                   // A stage = kseq % kAStages2, its use count
-    for (int tile = tile0; tile_live(tile); tile += tstep)
-      for (int ps = ps0; ps < ps1; ++ps, ++pseq) {
+    for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         if (!(P.exp_flags & 4)) {
           if (kPair) { if (!mbar_try_wait_cluster(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1)) mbar_wait_cluster(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201); }
           else mbar_wait<1>(smem_u32(&bars->acc_empty), (pseq & 1) ^ 1, P.status, 201);
@@ -440,7 +426,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       c.ks += kSets;
       if (c.ks >= kKS) {
         c.ks -= kKS;
-        if (++c.ps >= ps1) { c.ps = ps0; c.tile += tstep; return true; }
+        if (++c.ps >= P.passes) { c.ps = 0; c.tile += gridDim.x; return true; }
       }
       return false;
     };
@@ -480,7 +466,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       }
     };
 
-    Cursor ic{tile0, ps0, set};                        // issue cursor, kDepth own k-steps ahead of the consume cursor
+    Cursor ic{(int)blockIdx.x, 0, set};                // issue cursor, kDepth own k-steps ahead of the consume cursor
     auto issue = [&](uint32_t stage) {
       if (ic.tile < num_tiles && ic.ks < kKS - 1) {
         const uint32_t base = smem_u32(my_raw + (size_t)stage * kStageBytes);
@@ -514,7 +500,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 #pragma unroll
     for (int d = 0; d < kDepth; ++d) issue(d);
 
-    Cursor cc{tile0, ps0, set};
+    Cursor cc{(int)blockIdx.x, 0, set};
     uint32_t mine = 0, kseq = set;                     // kseq: sequence number of my current k-step (A stage = kseq % 4)
     while (tile_live(cc.tile)) {
       const uint32_t stage = mine % kDepth;
@@ -598,13 +584,13 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
     const uint32_t bar_done = 1 + q, bar_flushed = 5 + q, bar_clean = 9 + q;   // named barriers of this quarter's four warps
     uint32_t pseq = 0;
-    for (int tile = tile0; tile_live(tile); tile += tstep) {
+    for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x) {
       // Sparse mel contraction.  Every bin feeds the running pair of adjacent filters (cur, cur+1) of its chain; the host
       // table says how many filters close before each bin (bit j: one, predicated inline; bit 16+j: two or three, rare,
       // out of line).  A closed filter's partial sum is added to its parked sum (`old`, prefetched one close ahead; the
       // park rows start a tile zeroed).  The filters still open at the end of a chain are shared with the next chain, so
       // they go through s_fl and chain 0's warp adds them once all four chains of the quarter are done.
-      for (int ps = ps0; ps < ps1; ++ps, ++pseq) {
+      for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         float run_lo = 0.f, run_hi = 0.f;
         uint32_t pa = pa0 + 4u * (uint32_t)P.cstart[ps * kChains + ch];
         float old = ld_s(pa);
@@ -739,30 +725,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         }
         // nobody starts the next scan (or the log pass) before the open pairs are in the park rows
         asm volatile("bar.sync %0, %1;" ::"r"(bar_flushed), "n"(32 * kChains) : "memory");
-        bool do_log = ps == P.passes - 1;
-        const float* part_tile = nullptr;
-        if constexpr (kSplit) {
-          // tail split: this CTA computed ONE pass of the tile.  Its raw mel sums go to the tile's scratch; the CTA whose
-          // ticket completes the tile sums the passes in pass order (fixed order: deterministic) and runs the log pass
-          __shared__ int s_split_last;
-          const int tl = tile - P.split_tile0;
-          float* part = P.split_part + ((size_t)(tl * P.passes + ps) * kTileM) * P.n_mels;
-          for (int rr = (32 * ch) / kChains; rr < (32 * (ch + 1)) / kChains; ++rr) {
-            float* parked = s_park + (q * 32 + rr) * park_pitch + lane;
-            float* dstp = part + (size_t)(q * 32 + rr) * P.n_mels + lane;
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              if (lane + 32 * k < P.n_mels) { dstp[32 * k] = parked[32 * k]; parked[32 * k] = 0.f; }
-          }
-          __threadfence();
-          asm volatile("bar.sync 13, %0;" ::"n"(32 * kEpiWarps) : "memory");
-          if (warp == kWarpEpi02 && lane == 0) s_split_last = atomicAdd(P.split_cnt + tl, 1) == P.passes - 1;
-          asm volatile("bar.sync 13, %0;" ::"n"(32 * kEpiWarps) : "memory");
-          do_log = s_split_last != 0;
-          if (do_log) __threadfence();
-          part_tile = P.split_part + (size_t)tl * P.passes * kTileM * P.n_mels;
-        }
-        if (do_log) {
+        if (ps == P.passes - 1) {
           // raw mel sums -> log(max(., clamp)) / norm.  Each of the quarter's four warps takes 8 of its 32 rows: coalesced
           // output rows, 2 rows x up to 4 columns per lane in flight (independent logf / division chains); the park rows
           // are handed back zeroed for the next tile
@@ -786,16 +749,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 v[i][k] = 1.f;
-                if (mine && lane + 32 * k < P.n_mels) {
-                  if constexpr (kSplit) {
-                    float acc = 0.f;
-                    for (int pp = 0; pp < P.passes; ++pp)
-                      acc += __ldcg(part_tile + ((size_t)pp * kTileM + q * 32 + rr0 + i) * P.n_mels + lane + 32 * k);
-                    v[i][k] = acc;
-                  } else {
-                    v[i][k] = parked[32 * k]; parked[32 * k] = 0.f;
-                  }
-                }
+                if (mine && lane + 32 * k < P.n_mels) { v[i][k] = parked[32 * k]; parked[32 * k] = 0.f; }
               }
             }
 #pragma unroll
@@ -866,7 +820,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         P.stat_acc[i] += (double)tot * (sq ? 1.0 / 1073741824.0 : 1.0 / 4294967296.0);
       }
       if (threadIdx.x == 0) {
-        if (P.stat_count) P.stat_acc[2 * P.n_mels] += (double)P.frame_off[P.B];
+        P.stat_acc[2 * P.n_mels] += (double)P.frame_off[P.B];
         P.stat_ws[2 * kMaxMels] = 0ull;
       }
     }

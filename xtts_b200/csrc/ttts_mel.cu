@@ -480,8 +480,6 @@ struct Workspace {
   float* xp;            // [B][Lp]   (k_simt and unaligned inputs only)
   float* edge;          // [B][kEdgeClip] reflect-padded samples of each clip's first and last frames
   unsigned long long* stat;  // [2 * kMaxMels + 1] fixed-point statistics of one launch + CTA ticket (ttts_mel_forward_stats)
-  int* split_cnt;       // [num_sms] arrival tickets of the tail split (k_logmel2<.., kSplit>), zeroed by k_prep
-  float* split_part;    // [<= num_sms tiles x passes][128][n_mels] per-pass raw mel sums of the split tiles
   int64_t Lp;
   size_t bytes;
 };
@@ -496,8 +494,6 @@ Workspace carve(const ttts_mel_plan* p, void* base, int B, int64_t Lmax, bool di
   char* b = (char*)base;
   w.status = (int32_t*)(b + off); off += 256;
   w.stat = (unsigned long long*)(b + off); off += align_up((size_t)(2 * kMaxMels + 1) * 8, 256);
-  w.split_cnt = (int*)(b + off); off += align_up((size_t)(p->num_sms + 2) * 4, 256);
-  w.split_part = (float*)(b + off); off += align_up((size_t)(p->num_sms + 2) * kTileM * p->cfg.n_mels * 4, 256);
   w.frame_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.group_off = (int64_t*)(b + off); off += align_up((size_t)(B + 1) * 8, 256);
   w.n_frames = (int32_t*)(b + off); off += align_up((size_t)B * 4, 256);
@@ -681,8 +677,7 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
                                                int Tmax, int32_t* __restrict__ n_frames,
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
                                                int64_t* __restrict__ group_off, int32_t* __restrict__ status,
-                                               unsigned long long* __restrict__ stat_ws,
-                                               int* __restrict__ split_cnt, int n_split) {
+                                               unsigned long long* __restrict__ stat_ws) {
   asm volatile("griddepcontrol.launch_dependents;");   // the fused kernel may start its prologue (it waits for this grid's end)
   if (blockIdx.x > 0) {
     clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, (blockIdx.x - 1) / kPrepSplit,
@@ -693,7 +688,6 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
   const int tid = threadIdx.x;
   if (tid == 0) *status = 0;
   if (stat_ws && tid <= 2 * kMaxMels) stat_ws[tid] = 0ull;
-  if (split_cnt && tid < n_split) split_cnt[tid] = 0;
   __syncthreads();
   if (!lengths) {                           // dense batch: closed forms, no scan
     int err = 0;
@@ -1386,7 +1380,7 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   const bool direct = in_place;
   k_prep<<<kPrepSplit * B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
                                      p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status,
-                                     stat_acc ? w.stat : nullptr, w.split_cnt, p->num_sms + 2);
+                                     stat_acc ? w.stat : nullptr);
   ++g_launches;
   if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
@@ -1428,52 +1422,25 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
       const int rc = ensure_dynamic_smem(kern, (dbg_reim ? 4 : pair ? 2 : 0) + (pw1 ? 1 : 0), p->device, smem);
       if (rc != TTTS_MEL_OK) return rc;
     }
-    // Tail split (dense batches, CTA pairs): with TP tile pairs over CP CTA pairs the last round holds rem = TP mod CP tile
-    // pairs; when rem x passes <= CP those tile pairs are dealt one PASS per CTA pair by a second launch of the kSplit
-    // instantiation (a part-filled last round of `passes` passes becomes one pass plus a per-tile combine).  The host
-    // knows TP only for dense batches (ragged frame counts live on the device).
-    const int grid_main = pair ? (p->num_sms & ~1) : p->num_sms;
-    int split_units = 0;
-    P.tile_limit = 0x7fffffff; P.split_tile0 = 0; P.split_part = w.split_part; P.split_cnt = w.split_cnt; P.stat_count = 1;
-    if (pair && !lengths && P.passes >= 2 && !(TTTS_EXP_FLAGS() & 256)) {
-      const long long tiles = ((long long)B * P.G_uniform + 3) / 4, TP = (tiles + 1) / 2, CP = grid_main / 2;
-      const long long full = TP / CP, rem = TP - full * CP;
-      if (rem > 0 && rem * P.passes <= CP && 2 * rem <= p->num_sms + 2) {
-        split_units = (int)(rem * P.passes);
-        P.tile_limit = (int)(2 * full * CP);
-        P.split_tile0 = P.tile_limit;
-      }
-    }
     ProfileRing& pr = const_cast<ttts_mel_plan*>(p)->prof;
     const int pslot = pr.capacity > 0 ? pr.count.fetch_add(1) : -1;
     const bool prof = pslot >= 0 && pslot < pr.capacity;
     if (prof) cudaEventRecord(pr.start[pslot], stream);
-    cudaLaunchAttribute at[2];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // the prologue overlaps the grid in front (k_prep)
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    at[1].id = cudaLaunchAttributeClusterDimension;                  // CTA pair = the two SMs of a TPC
-    at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
-    if (P.tile_limit > 0) {
+    {
+      // programmatic dependent launch behind k_prep: the prologue of the persistent kernel overlaps it
       cudaLaunchConfig_t lc{};
-      lc.gridDim = dim3((unsigned)grid_main); lc.blockDim = dim3(f2::kThreads2);
+      lc.gridDim = dim3((unsigned)(pair ? p->num_sms & ~1 : p->num_sms)); lc.blockDim = dim3(f2::kThreads2);
       lc.dynamicSmemBytes = smem; lc.stream = stream;
+      cudaLaunchAttribute at[2];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      at[1].id = cudaLaunchAttributeClusterDimension;           // CTA pair = the two SMs of a TPC
+      at[1].val.clusterDim.x = 2; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
       lc.attrs = at; lc.numAttrs = pair ? 2 : 1;
       CUDA_TRY(cudaLaunchKernelEx(&lc, kern, P));
-      ++g_launches;
-      P.stat_count = 0;                                              // the frame count is added once per forward
-    }
-    if (split_units > 0) {
-      void (*kern_s)(const f2::Params) = pw1 ? k_logmel2<true, false, true, true> : k_logmel2<false, false, true, true>;
-      const int rc = ensure_dynamic_smem(kern_s, 6 + (pw1 ? 1 : 0), p->device, smem);
-      if (rc != TTTS_MEL_OK) return rc;
-      cudaLaunchConfig_t lc{};
-      lc.gridDim = dim3((unsigned)(2 * split_units)); lc.blockDim = dim3(f2::kThreads2);
-      lc.dynamicSmemBytes = smem; lc.stream = stream;
-      lc.attrs = at; lc.numAttrs = 2;
-      CUDA_TRY(cudaLaunchKernelEx(&lc, kern_s, P));
-      ++g_launches;
     }
     if (prof) cudaEventRecord(pr.stop[pslot], stream);
+    ++g_launches;
   } else if (impl == Impl::Tcgen05) {
     if (stat_acc) return fail(TTTS_MEL_EINVAL, "fused statistics need the k_logmel2 kernel");
     LogmelParams P{};
