@@ -119,6 +119,27 @@ int ttts_mel_forward_stats(const ttts_mel_plan* plan, const float* wav_dev, int6
                            float* mel_out_dev, int32_t* n_frames_dev_or_null, uint8_t* mask_dev_or_null,
                            void* workspace_dev, size_t workspace_bytes, void* stream, double* acc_dev);
 
+/* ttts_mel_forward without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The workspace of the call (status word, frame / group offsets, frame counts,
+ * the reflect-padded edge samples and, for inputs the kernel cannot read in place, the padded copy) lives in ONE
+ * file-scope `static __device__` array of TTTS_MEL_STATIC_WS_BYTES that every GPU loading the library holds until the
+ * process exits.  The call makes no cudaMalloc / cudaFree / allocating library call; the plan must exist already.
+ *   - a batch whose workspace (ttts_mel_workspace_bytes_for) exceeds TTTS_MEL_STATIC_WS_BYTES is rejected with
+ *     TTTS_MEL_ENOMEM and a message naming both sizes; use ttts_mel_forward with a caller workspace for those
+ *   - every call on a device shares the array and finds the previous call's contents in it; k_prep rewrites every word
+ *     the kernels read (status, offsets, counts, edges) at the start of each call, so nothing has to be cleared by the
+ *     caller -- but two calls that OVERLAP on the GPU (different streams, or graph branches) race on it and are not
+ *     supported: serialise them on one stream
+ *   - workspace_out_or_null receives the device address of the array (after the library resolved it with
+ *     cudaGetSymbolAddress on the current device), which is what ttts_mel_status() takes
+ * All other arguments and the results are those of ttts_mel_forward, bit for bit. */
+#define TTTS_MEL_STATIC_WS_BYTES (8u << 20)
+int ttts_mel_forward_static(const ttts_mel_plan* plan, const float* wav_dev, int64_t row_stride,
+                            const int64_t* lengths_dev_or_null, int32_t B, int64_t Lmax, int32_t Tmax,
+                            float* mel_out_dev, int32_t* n_frames_dev_or_null, uint8_t* mask_dev_or_null,
+                            void* stream, const void** workspace_out_or_null);
+
 /* sizeof(ttts_mel_config) as the library was built: a binding asserts its own struct against it. */
 size_t ttts_mel_config_size(void);
 

@@ -44,6 +44,7 @@ SYMBOLS = {
     "ttts_mel_workspace_bytes_for": (c_size_t, [c_void_p, c_int32, c_int64, c_void_p, c_int64]),
     "ttts_mel_forward": (ctypes.c_int, _FWD_ARGS),
     "ttts_mel_forward_stats": (ctypes.c_int, _FWD_ARGS + [c_void_p]),
+    "ttts_mel_forward_static": (ctypes.c_int, _FWD_ARGS[:10] + [c_void_p, POINTER(c_void_p)]),
     "ttts_mel_config_size": (c_size_t, []),
     "ttts_mel_first_bin": (c_int32, [c_void_p]),
     "ttts_mel_num_bins": (c_int32, [c_void_p]),

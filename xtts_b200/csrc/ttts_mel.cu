@@ -1503,6 +1503,55 @@ extern "C" int ttts_mel_forward_stats(const ttts_mel_plan* p, const float* wav, 
                       Impl::Tcgen05, nullptr, acc);
 }
 
+// ------------------------------------------------------------------------------------------
+// ttts_mel_forward_static: the workspace in a file-scope device array (no allocation anywhere on the call path).
+// No counterpart in the reference (include/ttts_mel.h).
+// In HOST code `g_static_ws` is only a handle for cudaGetSymbolAddress -- never a device address: the address is resolved
+// once per device, with that device current, and it is that pointer the kernels get.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_ws[TTTS_MEL_STATIC_WS_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kStaticMaxDevices] = {};
+
+int static_workspace(int device, void** out) {
+  if (device < 0 || device >= kStaticMaxDevices) return fail(TTTS_MEL_EINVAL, "device %d out of range", device);
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_ws);     // the current device is `device` (checked by the caller)
+    if (e != cudaSuccess || !ptr)
+      return fail(TTTS_MEL_ECUDA, "cudaGetSymbolAddress(static workspace) on device %d: %s", device, cudaGetErrorString(e));
+    g_static_ptr[device] = ptr;
+  }
+  *out = g_static_ptr[device];
+  return TTTS_MEL_OK;
+}
+}  // namespace
+
+extern "C" int ttts_mel_forward_static(const ttts_mel_plan* p, const float* wav, int64_t row_stride,
+                                       const int64_t* lengths, int32_t B, int64_t Lmax, int32_t Tmax, float* out,
+                                       int32_t* n_frames, uint8_t* mask, void* stream, const void** ws_out) {
+  if (ws_out) *ws_out = nullptr;
+  if (!p || !wav || !out) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || Lmax <= 0 || Tmax <= 0) return fail(TTTS_MEL_EINVAL, "empty batch (B=%d Lmax=%lld Tmax=%d)", B, (long long)Lmax, Tmax);
+  const size_t need = carve(p, nullptr, B, Lmax, reads_in_place(wav, row_stride, B)).bytes;
+  if (need > (size_t)TTTS_MEL_STATIC_WS_BYTES)
+    return fail(TTTS_MEL_ENOMEM, "this batch needs a %zu-byte workspace, the static one holds %zu: call ttts_mel_forward "
+                "with a caller workspace", need, (size_t)TTTS_MEL_STATIC_WS_BYTES);
+  int cur_dev = -1;
+  CUDA_TRY(cudaGetDevice(&cur_dev));
+  if (cur_dev != p->device) return fail(TTTS_MEL_EINVAL, "plan lives on device %d, the current device is %d", p->device, cur_dev);
+  void* ws = nullptr;
+  const int rc = static_workspace(cur_dev, &ws);
+  if (rc != TTTS_MEL_OK) return rc;
+  if (ws_out) *ws_out = ws;
+  return forward_impl(p, wav, row_stride, lengths, B, Lmax, Tmax, out, n_frames, mask, ws, (size_t)TTTS_MEL_STATIC_WS_BYTES,
+                      stream, Impl::Tcgen05, nullptr);
+}
+
 extern "C" size_t ttts_mel_config_size(void) { return sizeof(ttts_mel_config); }
 
 #ifdef TTTS_MEL_LAB
