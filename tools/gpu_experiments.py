@@ -19,7 +19,8 @@ else:
 names = {0: "full", 1: "no A handoff", 2: "no basis loads", 4: "no epilogue", 3: "MMA+epilogue only", 5: "no A, no epi",
          6: "no basis, no epi", 7: "MMA issue only", 8: "no drain math", 16: "no log pass", 24: "TMEM drain only", 32: "no MMAs", 36: "no MMAs, no epilogue", 38: "converters only (no MMA/basis/epi)", 34: "no MMAs, no basis",
          35: "epilogue only", 43: "epilogue only, no drain math", 51: "epilogue only, no log pass", 59: "epilogue only: TMEM loads + barriers",
-         71: "MMA issue only, no per-k-step commits", 39: "bare issue loop (no MMAs)", 103: "bare loop, no commits"}
+         71: "MMA issue only, no per-k-step commits", 39: "bare issue loop (no MMAs)", 103: "bare loop, no commits",
+         128: "no raw-audio loads", 132: "no raw loads, no epilogue", 134: "no raw, no basis, no epilogue"}
 FLAGS = [int(a) for a in sys.argv[1:]] or [0, 4, 8, 16, 24, 7, 32, 36, 38, 34, 0]
 for flags in FLAGS:
     lib.ttts_mel_set_experiment(flags)

@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 
     Cursor ic{(int)blockIdx.x, 0, set};                // issue cursor, kDepth own k-steps ahead of the consume cursor
     auto issue = [&](uint32_t stage) {
-      if (ic.tile < num_tiles && ic.ks < kKS - 1) {
+      if (ic.tile < num_tiles && ic.ks < kKS - 1 && !(P.exp_flags & 128)) {   // 128: timing experiment, no raw-audio loads
         const uint32_t base = smem_u32(my_raw + (size_t)stage * kStageBytes);
         const int adv = kKStep * ic.ks;
         if (plain) {                                   // warp-uniform: interior groups (all but the first / last of a clip)
