@@ -214,8 +214,10 @@ def test_pcm16_corpus_sweep_matches_clip_by_clip_reference(tmp_path):
     assert sweep.run_files(lambda idx, m: calls.append(idx), mel_pth_sink(paths), done=mel_pth_done(paths)) == 0
     assert calls == []
     # the module that owns the plan still applies ITS norms (none here) after the sweep touched the plan
-    x = torch.rand(1, 24000, device="cuda:0") * 2 - 1
-    assert float((mod(x) - orc.callsite_logmel(x.cpu(), orc.V2, None).to("cuda:0")).abs().max()) <= 1e-4
+    # (V2's bar, DESIGN section 2: 1e-4 on the log-mel, or 2e-5 absolute on the mel magnitude where a one-bin filter is small)
+    x = torch.rand(1, 24000, device="cuda:0", generator=torch.Generator(device="cuda:0").manual_seed(7)) * 2 - 1
+    ref = orc.callsite_logmel(x.cpu(), orc.V2, None).to("cuda:0")
+    assert bool(((mod(x) - ref).abs() <= torch.maximum(torch.full_like(ref, 1e-4), 2e-5 / ref.exp())).all())
 
 
 def test_numa_binding_reads_sysfs_and_degrades_quietly(tmp_path, monkeypatch):
