@@ -5,6 +5,8 @@ sys.path.insert(0, ROOT)
 import torch
 from xtts_b200 import MelPlan, _cabi
 dev = torch.device("cuda:0")
+if os.environ.get("TTTS_LAB_SO"):       # time another build of the lab library (e.g. the previous commit's)
+    _cabi.LAB_PATH = os.environ["TTTS_LAB_SO"]
 lib = _cabi.lab()          # leg removal exists in the lab build only (include/ttts_mel_lab.h)
 V2 = "--v2" in sys.argv          # the MelSpectrogramFeatures parametrisation (24 kHz, 100 mel, 512 live bins, power 1)
 if V2:
