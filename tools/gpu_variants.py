@@ -25,7 +25,10 @@ def worker(so):
         "v2": (dict(sample_rate=24000, n_fft=1024, hop_length=256, win_length=1024, n_mels=100, f_min=0, f_max=None,
                     power=1.0, norm=None, clamp=1e-7), 240000),
     }
+    only = os.environ.get("VARIANTS_CASES")          # e.g. "v2": variants built for one parametrisation only
     for name, (kw, L) in cases.items():
+        if only and name not in only.split(","):
+            continue
         plan = MelPlan(device=dev, **kw)
         xs = [torch.rand(64, L, device=dev, generator=g) * 2 - 1 for _ in range(4)]
         for i in range(5):
@@ -47,6 +50,18 @@ def worker(so):
         plan.profile_enable(0)
         res[name + "_us_median"] = round(ms[k // 2] * 1e3, 2)
         res[name + "_us_min"] = round(ms[0] * 1e3, 2)
+        if os.environ.get("VARIANTS_SUSTAINED"):
+            # the bench's regime: thousands of launches back to back, the board at its power cap (SM clock ~1.75 GHz)
+            plan.profile_enable(0)
+            ns = int(os.environ["VARIANTS_SUSTAINED"])
+            for rep in range(2):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for i in range(ns):
+                    plan.forward(xs[i & 3])
+                b.record()
+                torch.cuda.synchronize()
+            res[name + "_sustained_step_us"] = round(a.elapsed_time(b) / ns * 1e3, 2)
         plan.status()
     print("RESULT " + json.dumps(res), flush=True)
 

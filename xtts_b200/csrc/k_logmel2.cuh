@@ -33,7 +33,14 @@ namespace f2 {
 #define F2_CHAINS 4
 #endif
 constexpr int kSets = F2_SETS;                   // converter sets: set s serves the k-steps with sequence number == s (mod kSets)
-constexpr int kAStages2 = 4;                     // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
+#ifndef F2_ASTAGES
+#define F2_ASTAGES 4
+#endif
+#ifndef F2_ACC_STRIDE
+#define F2_ACC_STRIDE kNBMax
+#endif
+constexpr int kAStages2 = F2_ASTAGES;            // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
+constexpr int kAccStride2 = F2_ACC_STRIDE;        // columns between the Re and Im accumulators; the A ring starts at twice that
                                                  // (8 stages in V2's spare columns: no gain, and the run-time depth cost V1 3 %: profiles/r2g_variants.txt)
 constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
@@ -80,9 +87,10 @@ constexpr int kBStages2 = 4;                      // basis ring depth (single CT
 #define F2_BSTAGES_PAIR 8
 #endif
 constexpr int kBStagesPair = F2_BSTAGES_PAIR;     // ... of a CTA pair (8 x 12 KB): the peer's half arrives through a relay
-constexpr int kColA2 = 2 * kNBMax;                // A ring behind the accumulators
+constexpr int kColA2 = 2 * kAccStride2;            // A ring behind the accumulators
+static_assert(kColA2 + 32 * kAStages2 <= 512, "TMEM columns");
 constexpr int kChains = F2_CHAINS;               // mel-scan chains per pass, one epilogue warp each (per lane quarter)
-static_assert(kThreads2 == 1024 && kAStages2 % 1 == 0, "4 misc + 4 kSets + 4 kChains warps must be 32");
+static_assert(kThreads2 <= 1024 && kAStages2 > kSets, "at most 32 warps; the operand ring is deeper than the number of converter sets");
 #ifndef F2_QR_UNROLL
 #define F2_QR_UNROLL 1
 #endif
@@ -184,6 +192,49 @@ __device__ __noinline__ void park_multi(uint32_t pa, float lo, float hi) {
   st_s(pa + 4, ld_s(pa + 4) + hi);
 }
 
+// ---- the mel scan of four consecutive bins (one tcgen05.ld round), specialised by the block's close pattern.
+// Which filters close before which bin is warp-uniform and known to the plan, so instead of testing two mask bits and
+// stepping over seven predicated-off instructions at EVERY bin (round 2's ncu: ~25 issued instructions per bin, the
+// accumulator drain issue-bound at ~3.7 us per pass), the block's 4-bit pattern selects one of 16 straight-line bodies:
+// 8 FMAs plus 4 instructions per close (the shifts run_lo = run_hi, run_hi = 0 fold into the FMAs).
+struct ScanState { float run_lo, run_hi, old; uint32_t pa; };
+
+template <int NIB>
+__device__ __forceinline__ void scan4_body(ScanState& s, const float (&pw)[4], const float4& wa, const float4& wb) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (NIB & (1 << j)) {                      // one filter closes before this bin
+      st_s(s.pa, s.old + s.run_lo);
+      s.run_lo = s.run_hi; s.run_hi = 0.f;
+      s.pa += 4;
+      s.old = ld_s(s.pa);                      // consumed at the next close
+    }
+    const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
+    const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
+    s.run_lo = fmaf(wl, pw[j], s.run_lo);
+    s.run_hi = fmaf(wh, pw[j], s.run_hi);
+  }
+}
+__device__ __forceinline__ void scan4_switch(ScanState& s, const float (&pw)[4], const float4& wa, const float4& wb, uint32_t nib) {
+  switch (nib) {
+    case 0: scan4_body<0>(s, pw, wa, wb); break;
+    case 1: scan4_body<1>(s, pw, wa, wb); break;
+    case 2: scan4_body<2>(s, pw, wa, wb); break;
+    case 3: scan4_body<3>(s, pw, wa, wb); break;
+    case 4: scan4_body<4>(s, pw, wa, wb); break;
+    case 5: scan4_body<5>(s, pw, wa, wb); break;
+    case 6: scan4_body<6>(s, pw, wa, wb); break;
+    case 7: scan4_body<7>(s, pw, wa, wb); break;
+    case 8: scan4_body<8>(s, pw, wa, wb); break;
+    case 9: scan4_body<9>(s, pw, wa, wb); break;
+    case 10: scan4_body<10>(s, pw, wa, wb); break;
+    case 11: scan4_body<11>(s, pw, wa, wb); break;
+    case 12: scan4_body<12>(s, pw, wa, wb); break;
+    case 13: scan4_body<13>(s, pw, wa, wb); break;
+    case 14: scan4_body<14>(s, pw, wa, wb); break;
+    default: scan4_body<15>(s, pw, wa, wb); break;
+  }
+}
 // ---- CTA-pair (cta_group::2) helpers
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -346,7 +397,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const uint32_t desc_lo0 = (((uint32_t)nbh * 16u) >> 4) << 16;  // LBO = nbh*16 B between the two k-halves
     const uint32_t arr16 = ((uint32_t)nbh * 32u) >> 4;          // one operand array, in 16 B units
     const uint32_t sb0 = smem_u32(s_b) >> 4, stage16 = b_stage_bytes >> 4;
-    const uint32_t d_re = tmem, d_im = tmem + kNBMax;
+    const uint32_t d_re = tmem, d_im = tmem + kAccStride2;
     uint32_t kseq = 0, pseq = 0;
     uint32_t as = 0, ause = 0;                                   // A stage = kseq % kAStages2, its use count
     for (int tile = blockIdx.x; tile_live(tile); tile += gridDim.x)
@@ -580,7 +631,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const int cb = nb / kChains;                       // bins per chain (multiple of 16)
-    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + kNBMax;
+    const uint32_t t_re = tmem + lane_addr + ch * cb, t_im = t_re + kAccStride2;
     const uint32_t pa0 = smem_u32(s_park + r * park_pitch);
     const uint32_t bar_done = 1 + q, bar_flushed = 5 + q, bar_clean = 9 + q;   // named barriers of this quarter's four warps
     uint32_t pseq = 0;
@@ -591,35 +642,85 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       // park rows start a tile zeroed).  The filters still open at the end of a chain are shared with the next chain, so
       // they go through s_fl and chain 0's warp adds them once all four chains of the quarter are done.
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
-        float run_lo = 0.f, run_hi = 0.f;
-        uint32_t pa = pa0 + 4u * (uint32_t)P.cstart[ps * kChains + ch];
-        float old = ld_s(pa);
+        ScanState sc;
+        sc.run_lo = 0.f; sc.run_hi = 0.f;
+        sc.pa = pa0 + 4u * (uint32_t)P.cstart[ps * kChains + ch];
+        sc.old = ld_s(sc.pa);
         const int bin_base = ps * nb + ch * cb;
         mbar_wait<3>(smem_u32(&bars->acc_full), pseq & 1, P.status, 501);
         tc_fence_after();
-        // scan of four consecutive bins whose power is in registers
+        // scan of four consecutive bins whose power is in registers.  Power plans (V1): the block's 4-bit close pattern
+        // selects one of 16 straight-line bodies (-2 % on the kernel, short runs and at the power cap alike:
+        // profiles/r2v, r2w); magnitude plans (V2) scan from registers at eight unrolled call sites, where the 16 bodies
+        // would have to go out of line (+1-2 %): they keep the predicated per-bin form.
         auto scan4 = [&](const float (&pw4)[4], uint32_t advq, int bin0) {
-          const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin0);
-          const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin0 + 2);
+          if (kPower1) {
+            const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin0);
+            const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin0 + 2);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (advq & (0x10000u << j)) {            // warp-uniform, rare: two or three filters close
-              const uint32_t cnt = (s_adv2[bin0 >> 4] >> (2 * ((bin0 & 15) + j))) & 3u;
-              park_multi(pa, run_lo, run_hi);
-              run_lo = 0.f; run_hi = 0.f;
-              pa += 4 * cnt;
-              old = ld_s(pa);
+            for (int j = 0; j < 4; ++j) {
+              if (advq & (0x10000u << j)) {            // warp-uniform, rare: two or three filters close
+                const uint32_t cnt = (s_adv2[bin0 >> 4] >> (2 * ((bin0 & 15) + j))) & 3u;
+                park_multi(sc.pa, sc.run_lo, sc.run_hi);
+                sc.run_lo = 0.f; sc.run_hi = 0.f;
+                sc.pa += 4 * cnt;
+                sc.old = ld_s(sc.pa);
+              }
+              if (advq & (1u << j)) {                  // warp-uniform: one filter closes before this bin
+                st_s(sc.pa, sc.old + sc.run_lo);
+                sc.run_lo = sc.run_hi; sc.run_hi = 0.f;
+                sc.pa += 4;
+                sc.old = ld_s(sc.pa);                     // consumed at the next close
+              }
+              const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
+              const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
+              sc.run_lo = fmaf(wl, pw4[j], sc.run_lo);
+              sc.run_hi = fmaf(wh, pw4[j], sc.run_hi);
             }
-            if (advq & (1u << j)) {                  // warp-uniform: one filter closes before this bin
-              st_s(pa, old + run_lo);
-              run_lo = run_hi; run_hi = 0.f;
-              pa += 4;
-              old = ld_s(pa);                        // consumed at the next close
+          } else if (advq & 0xf0000u) {                     // warp-uniform: some bin of the block has two or three filters
+                                                     // closing before it (the narrow low-frequency filters: all of
+                                                     // chain 0's first blocks) -- one four-way switch per bin
+            const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin0);
+            const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin0 + 2);
+            const uint32_t cnt8 = (s_adv2[bin0 >> 4] >> (2 * (bin0 & 15))) & 0xffu;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              switch ((cnt8 >> (2 * j)) & 3u) {
+                case 0: break;
+                case 1:
+                  st_s(sc.pa, sc.old + sc.run_lo);
+                  sc.run_lo = sc.run_hi; sc.run_hi = 0.f;
+                  sc.pa += 4;
+                  sc.old = ld_s(sc.pa);
+                  break;
+                case 2: {
+                  const float o2 = ld_s(sc.pa + 4);
+                  st_s(sc.pa, sc.old + sc.run_lo);
+                  st_s(sc.pa + 4, o2 + sc.run_hi);
+                  sc.run_lo = 0.f; sc.run_hi = 0.f;
+                  sc.pa += 8;
+                  sc.old = ld_s(sc.pa);
+                  break;
+                }
+                default: {
+                  const float o2 = ld_s(sc.pa + 4);
+                  st_s(sc.pa, sc.old + sc.run_lo);
+                  st_s(sc.pa + 4, o2 + sc.run_hi);
+                  sc.run_lo = 0.f; sc.run_hi = 0.f;
+                  sc.pa += 12;
+                  sc.old = ld_s(sc.pa);
+                  break;
+                }
+              }
+              const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
+              const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
+              sc.run_lo = fmaf(wl, pw4[j], sc.run_lo);
+              sc.run_hi = fmaf(wh, pw4[j], sc.run_hi);
             }
-            const float wl = j == 0 ? wa.x : j == 1 ? wa.z : j == 2 ? wb.x : wb.z;
-            const float wh = j == 0 ? wa.y : j == 1 ? wa.w : j == 2 ? wb.y : wb.w;
-            run_lo = fmaf(wl, pw4[j], run_lo);
-            run_hi = fmaf(wh, pw4[j], run_hi);
+          } else {
+            const float4 wa = *reinterpret_cast<const float4*>(s_melw + bin0);
+            const float4 wb = *reinterpret_cast<const float4*>(s_melw + bin0 + 2);
+            scan4_switch(sc, pw4, wa, wb, advq & 0xfu);
           }
         };
         auto power_of = [&](uint32_t re, uint32_t im) {
@@ -711,8 +812,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
         }
         // the pair still open at the end of my chain
         float* fl = s_fl + ((pseq & 1) * kChains + ch) * 2 * kTileM + r;
-        fl[0] = run_lo;
-        fl[kTileM] = run_hi;
+        fl[0] = sc.run_lo;
+        fl[kTileM] = sc.run_hi;
         if (ch != 0) {
           asm volatile("bar.arrive %0, %1;" ::"r"(bar_done), "n"(32 * kChains) : "memory");
         } else {
