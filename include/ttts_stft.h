@@ -38,6 +38,19 @@ int ttts_stft_magnitude(const float* y_dev, int64_t y_stride, int32_t row0, int3
                         int32_t nbins, float clamp, float power, int32_t to_db, float db_gain, float* out_dev,
                         void* stream);
 
+/* The rest of TorchMelSpectrogram.forward (ttts/utils/utils.py:509-522) for transform sizes the fused kernel of
+ * ttts_mel.h is not built for (any filter_length / hop_length / win_length the reference's constructor takes,
+ * utils.py:487-507): power -> matmul(spec^T, fb) (torchaudio _transforms.py:407-418) -> log(clamp(., clamp)) [/ mel_norms],
+ * written [B, Tmax, n_mels] like ttts_mel_forward.  Frames t >= n_frames[b] (or >= T) are zeros.
+ *   y_dev       rows as ttts_stft_magnitude reads them (re of bin k at column 2k, im at 2k + 1; frame t = row row0 + t)
+ *   fbT_dev     [n_mels, nbins] float32: the reference's filterbank, transposed
+ *   krange_dev  [n_mels, 2] int32: first / last bin with a non-zero weight of each filter (first > last: empty filter)
+ *   power       1 (sqrt(re^2 + im^2 + power_eps)) or 2 */
+int ttts_stft_logmel(const float* y_dev, int64_t y_stride, int32_t row0, int32_t n_cols, int32_t B, int32_t T,
+                     const int32_t* n_frames_dev_or_null, int32_t Tmax, int32_t nbins, const float* fbT_dev,
+                     const int32_t* krange_dev, int32_t n_mels, float power, float power_eps, float clamp,
+                     const float* norms_dev_or_null, float* out_dev, void* stream);
+
 /* spectral_ops.py:49-52 input side: complex spectrogram [B, N, T] (complex64 = float pairs) -> [B, T, 2N] rows
  * (re of bin k at column k, im at column N + k), the row layout the inverse contraction strides over. */
 int ttts_spec_pack(const float* spec_ri_dev, int32_t B, int32_t N, int32_t T, float* x_dev, void* stream);

@@ -584,3 +584,59 @@ def test_two_rank_nccl_sweep_statistics_equal_single_rank(dev):
     rel = np.abs(s0[:160] - one0[:160]) / np.abs(one0[:160])
     print(f"2-rank NCCL vs single rank: max relative difference {rel.max():.2e}")
     assert rel.max() <= 1e-12
+
+
+# ---- transform sizes other than 1024 / 256 (the reference's constructor takes any: utils.py:487-507) -- GeneralMelPlan:
+# reflect pad + the tcgen05 contraction + ttts_stft_logmel, through the same module and C ABI
+def _general_module(cfg_row):
+    from xtts_b200 import TorchMelSpectrogram
+    n_fft, hop, win, n_mels, fmin, fmax, sr, normalize, has_norms = (int(v) for v in cfg_row[:9])
+    m = TorchMelSpectrogram(filter_length=n_fft, hop_length=hop, win_length=win, n_mel_channels=n_mels, mel_fmin=fmin,
+                            mel_fmax=fmax, sampling_rate=sr, normalize=bool(normalize), mel_norm_file=None)
+    if has_norms:
+        m.mel_norms = torch.from_numpy(orc.default_mel_norms(n_mels))
+    cfg = orc.MelConfig(sample_rate=sr, n_fft=n_fft, hop=hop, win_length=win, n_mels=n_mels, f_min=float(fmin),
+                        f_max=float(fmax), normalized=bool(normalize))
+    return m, cfg, (orc.default_mel_norms(n_mels) if has_norms else None)
+
+
+def test_general_transform_sizes_match_the_reference_goldens(dev, golden_dir):
+    g = np.load(f"{golden_dir}/v1_general_shapes.npz")
+    names = [k[4:] for k in g.files if k.startswith("cfg_")]
+    assert len(names) == 5
+    for name in names:
+        row = g[f"cfg_{name}"]
+        m, cfg, _ = _general_module(row)
+        gauss, L, seed = int(row[9]), int(row[10]), int(row[11])
+        x = orc.synth("gauss" if gauss else "uniform", 2, L, seed)
+        y = m(torch.from_numpy(x).to(dev))
+        ref = g[f"y_{name}"]
+        assert tuple(y.shape) == ref.shape, name                       # bit-exact frame counts
+        assert y.stride() == (ref.shape[2] * ref.shape[1], 1, ref.shape[1]), name
+        err = float(np.abs(_np(y) - ref).max())
+        assert err <= TOL, (name, err)
+        y3 = m(torch.from_numpy(x).to(dev)[:, None, :])                # [B, 1, L] form
+        assert torch.equal(y3, y)
+
+
+def test_general_transform_sizes_ragged_batch_and_batch_size(dev):
+    row = np.array([2048, 512, 2048, 80, 0, 8000, 22050, 0, 1])
+    m, cfg, norms = _general_module(row)
+    lens = [40000, 1025, 2048, 33333, 12000, 40000]
+    x = orc.synth("uniform", len(lens), max(lens), 77)
+    ym, nf, mask = m(torch.from_numpy(x).to(dev), lengths=torch.tensor(lens))
+    rm, rn, rmask = orc.callsite_logmel_ragged(x, lens, cfg, norms)
+    assert nf.cpu().tolist() == rn.tolist() and np.array_equal(mask.cpu().numpy(), rmask)
+    assert float(np.abs(_np(ym) - rm.numpy()).max()) <= TOL
+    # device-resident lengths: same result, nothing validated on the host
+    ym2, nf2, mask2 = m(torch.from_numpy(x).to(dev), lengths=torch.tensor(lens, device=dev))
+    assert torch.equal(nf2, nf) and torch.equal(mask2, mask) and torch.equal(ym2[:, :, :ym.shape[2]], ym)
+    # 64 x 10 s at the size the headline uses: every value of a 4-clip sample against the reference's call
+    xb = torch.rand(64, 220500, device=dev, generator=torch.Generator(device=dev).manual_seed(5)) * 2 - 1
+    yb = m(xb)
+    assert tuple(yb.shape) == (64, 80, orc.frame_count(220500, cfg))
+    for b in (0, 17, 40, 63):
+        ref = orc.callsite_logmel(xb[b:b + 1].cpu().numpy(), cfg, norms).numpy()
+        assert float(np.abs(_np(yb[b:b + 1]) - ref).max()) <= TOL, b
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 1024, device=dev))                          # reflect pad 1024 needs more than 1024 samples

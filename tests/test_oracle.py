@@ -140,3 +140,23 @@ def test_v3_layers_agree_and_filterbank_restatement():
     a = orc.callsite_logmel(x, orc.V3).numpy()
     assert a.shape == (2, 80, 6000 // 256)
     assert np.abs(orc.restated_logmel(x, orc.V3) - a).max() <= 5e-5
+
+
+def test_general_shape_goldens_match_both_oracle_layers(golden_dir):
+    """tests/golden/v1_general_shapes.npz: the reference's TorchMelSpectrogram built with other filter_length / hop_length /
+    win_length / n_mel_channels / sampling_rate values (oracle/gen_golden_general.py)."""
+    g = np.load(f"{golden_dir}/v1_general_shapes.npz")
+    names = [k[4:] for k in g.files if k.startswith("cfg_")]
+    assert len(names) == 5
+    for name in names:
+        n_fft, hop, win, n_mels, fmin, fmax, sr, normalize, has_norms, gauss, L, seed = (int(v) for v in g[f"cfg_{name}"])
+        cfg = orc.MelConfig(sample_rate=sr, n_fft=n_fft, hop=hop, win_length=win, n_mels=n_mels, f_min=float(fmin),
+                            f_max=float(fmax), normalized=bool(normalize))
+        norms = orc.default_mel_norms(n_mels) if has_norms else None
+        x = orc.synth("gauss" if gauss else "uniform", 2, L, seed)
+        ref = g[f"y_{name}"]
+        y = orc.callsite_logmel(x, cfg, norms).numpy()
+        assert y.shape == ref.shape and np.array_equal(y, ref), name              # same call sequence: bit for bit
+        assert ref.shape[2] == orc.frame_count(L, cfg)
+        r = orc.restated_logmel(x, cfg, norms)
+        assert np.abs(r - ref).max() <= 2e-4, (name, float(np.abs(r - ref).max()))  # fp64 restatement vs the fp32 reference

@@ -68,6 +68,8 @@ SYMBOLS = {
     "ttts_reflect_pad": (ctypes.c_int, [c_void_p, c_int64, c_void_p, c_int32, c_int64, c_int32, c_void_p, c_int64, c_void_p]),
     "ttts_stft_magnitude": (ctypes.c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, c_float,
                                            c_int32, c_float, c_void_p, c_void_p]),
+    "ttts_stft_logmel": (ctypes.c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_int32, c_void_p, c_int32, c_int32,
+                                        c_void_p, c_void_p, c_int32, c_float, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "ttts_spec_pack": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "ttts_istft_overlap_add": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p, c_void_p,
                                               c_int64, c_void_p, c_void_p]),

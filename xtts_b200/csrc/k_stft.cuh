@@ -42,6 +42,52 @@ __global__ void __launch_bounds__(256) k_stft_mag(const float* __restrict__ y, l
   }
 }
 
+// General-shape log-mel behind the same contraction (TorchMelSpectrogram with filter_length / hop_length other than
+// 1024 / 256, ttts/utils/utils.py:487-507: torchaudio MelSpectrogram takes any n_fft / hop / win; the fused kernel
+// k_logmel2 is built for hop = n_fft / 4 = 256 only).  y rows as k_stft_mag reads them; per block kFR frames:
+//   phase 1  power (|X|^2, or sqrt(|X|^2 + eps) for the magnitude plans) of every bin -> shared memory, coalesced float2 loads
+//   phase 2  one thread per (frame, mel): sum over the filter's own bin range [k_lo, k_hi] of fbT[m][k] * P[k] (ascending k),
+//            log(max(., clamp)) [/ norms[m]] -> out[b][t][m]; frames at or past n_frames[b] are zeros (the collate contract)
+template <int kFR>
+__global__ void __launch_bounds__(256) k_stft_logmel(const float* __restrict__ y, long long y_stride, int row0, int n_cols,
+                                                     const int32_t* __restrict__ n_frames, int T, int Tmax, int nbins,
+                                                     const float* __restrict__ fbT, const int2* __restrict__ krange,
+                                                     int n_mels, int power1, float eps, float clamp,
+                                                     const float* __restrict__ norms, float* __restrict__ out) {
+  extern __shared__ float s_pw[];                               // [kFR][nbins + 1]
+  const int pitch = nbins + 1;
+  const int b = blockIdx.y, t0 = blockIdx.x * kFR;
+  const int nf = n_frames ? min(n_frames[b], T) : T;
+  const float* yb = y + (long long)b * y_stride;
+  for (int r = 0; r < kFR; ++r) {
+    const int t = t0 + r;
+    if (t >= nf) break;                                         // block-uniform
+    const float* row = yb + (long long)(row0 + t) * n_cols;
+    for (int k = threadIdx.x; k < nbins; k += 256) {
+      const float2 v = *reinterpret_cast<const float2*>(row + 2 * k);
+      float pw = fmaf(v.x, v.x, v.y * v.y);
+      if (power1) pw = sqrtf(pw + eps);
+      s_pw[r * pitch + k] = pw;
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < kFR * n_mels; idx += 256) {
+    const int r = idx / n_mels, m = idx - r * n_mels, t = t0 + r;
+    if (t >= Tmax) continue;
+    float v = 0.f;
+    if (t < nf) {
+      const int2 kr = krange[m];
+      const float* w = fbT + (long long)m * nbins;
+      const float* pw = s_pw + r * pitch;
+      float acc = 0.f;
+      for (int k = kr.x; k <= kr.y; ++k) acc = fmaf(__ldg(w + k), pw[k], acc);
+      v = logf(fmaxf(acc, clamp));
+      if (norms) v = v / norms[m];
+    }
+    out[((long long)b * Tmax + t) * n_mels + m] = v;
+  }
+}
+
 // spec [B][N][T] complex64 (float pairs) -> x [B][T][2N]: re of bin k at column k, im at column N + k
 __global__ void __launch_bounds__(256) k_spec_pack(const float2* __restrict__ spec, int N, int T, float* __restrict__ x) {
   __shared__ float2 tile[32][33];
@@ -113,6 +159,36 @@ extern "C" int ttts_stft_magnitude(const float* y, int64_t y_stride, int32_t row
     return fail(TTTS_MEL_EINVAL, "stft magnitude: bad geometry");
   dim3 grid((unsigned)((T + 31) / 32), (unsigned)((nbins + 31) / 32), (unsigned)B);
   stft::k_stft_mag<<<grid, 256, 0, (cudaStream_t)stream>>>(y, y_stride, row0, n_cols, T, nbins, clamp, power, to_db, db_gain, out);
+  CUDA_TRY(cudaGetLastError());
+  return TTTS_MEL_OK;
+}
+
+extern "C" int ttts_stft_logmel(const float* y, int64_t y_stride, int32_t row0, int32_t n_cols, int32_t B, int32_t T,
+                                const int32_t* n_frames, int32_t Tmax, int32_t nbins, const float* fbT,
+                                const int32_t* krange, int32_t n_mels, float power, float power_eps, float clamp,
+                                const float* norms, float* out, void* stream) {
+  if (!y || !fbT || !krange || !out) return fail(TTTS_MEL_EINVAL, "null argument");
+  if (B <= 0 || T <= 0 || Tmax < T || nbins <= 0 || n_mels <= 0 || n_cols < 2 * nbins || (n_cols & 1) || row0 < 0 ||
+      (((uintptr_t)y | (uintptr_t)(y_stride * 4) | (uintptr_t)krange) & 7))
+    return fail(TTTS_MEL_EINVAL, "stft log-mel: bad geometry");
+  if (!(power == 1.0f || power == 2.0f) || !(clamp > 0.f) || !(power_eps >= 0.f))
+    return fail(TTTS_MEL_EINVAL, "stft log-mel: power must be 1 or 2, clamp > 0, power_eps >= 0");
+  constexpr int kFR = 8;
+  const size_t smem = (size_t)kFR * (nbins + 1) * sizeof(float);
+  if (smem > 200 * 1024) return fail(TTTS_MEL_EINVAL, "stft log-mel: %d bins do not fit in shared memory", nbins);
+  if (smem > 48 * 1024) {
+    static std::atomic<size_t> granted[64];
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || granted[dev].load() < smem) {
+      CUDA_TRY(cudaFuncSetAttribute(stft::k_stft_logmel<kFR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (dev >= 0 && dev < 64) granted[dev].store(smem);
+    }
+  }
+  dim3 grid((unsigned)((Tmax + kFR - 1) / kFR), (unsigned)B);
+  stft::k_stft_logmel<kFR><<<grid, 256, smem, (cudaStream_t)stream>>>(y, y_stride, row0, n_cols, n_frames, T, Tmax, nbins, fbT,
+                                                                    reinterpret_cast<const int2*>(krange), n_mels,
+                                                                    power == 1.0f ? 1 : 0, power_eps, clamp, norms, out);
   CUDA_TRY(cudaGetLastError());
   return TTTS_MEL_OK;
 }

@@ -205,6 +205,133 @@ class MelPlan:
                 acc.data_ptr(), stream))
 
 
+class GeneralMelPlan:
+    """The same call as ``MelPlan.forward`` for transform sizes the fused kernel is not built for (the reference's
+    constructor takes any filter_length / hop_length / win_length, utils.py:487-507; every shipped config uses 1024 / 256 and
+    runs on ``MelPlan``).  Three launches instead of one fused kernel: per-clip reflect pad (``ttts_reflect_pad``), the
+    windowed DFT as the library's dense tcgen05 contraction (``ttts_resample_forward``, 3xTF32, as ``stft.TorchSTFT``),
+    and ``ttts_stft_logmel`` (power -> filterbank -> log(clamp) -> / mel_norms).  The spectrum makes one HBM round trip."""
+
+    def __init__(self, *, sample_rate: int, n_fft: int, hop_length: int, win_length: Optional[int], n_mels: int,
+                 f_min: float, f_max: Optional[float], power: float, norm: Optional[str], mel_scale: str = "htk",
+                 normalized: bool = False, clamp: float = 1e-5, center: bool = True, pre_pad: int = 0,
+                 power_eps: float = 0.0, fb: Optional[torch.Tensor] = None,
+                 device: Union[str, torch.device, int] = "cuda", lab: bool = False):
+        from .stft import _Contraction, windowed_dft_taps
+        self._lib = _cabi.lib()
+        self.lab = False
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("GeneralMelPlan needs a CUDA device (sm_100a); there is no CPU fallback")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.n_fft, self.hop, self.n_mels = int(n_fft), int(hop_length), int(n_mels)
+        self.win_length = int(win_length) if win_length is not None else self.n_fft
+        N, H, W = self.n_fft, self.hop, self.win_length
+        if N % 8 or W > N or (N - W) % 2 or H > W or (W - H) % 2 or H < 1:
+            raise NotImplementedError(f"general log-mel path: need n_fft % 8 == 0, hop <= win_length <= n_fft and "
+                                      f"(n_fft - win_length), (win_length - hop) even; got {N} / {H} / {W}")
+        self.pad = N // 2 if center else int(pre_pad)
+        self.power, self.clamp, self.power_eps = float(power), float(clamp), float(power_eps)
+        if self.power not in (1.0, 2.0):
+            raise ValueError("power must be 1 or 2")
+        f_max = float(f_max) if f_max is not None else float(sample_rate // 2)
+        if fb is None:
+            fb = melscale_fbanks(N // 2 + 1, float(f_min), f_max, self.n_mels, int(sample_rate), norm, mel_scale)
+        self.fb = fb.to(torch.float32).contiguous()          # [n_freqs, n_mels]
+        window = torch.hann_window(W, periodic=True, dtype=torch.float32)   # torchaudio's default window_fn
+        self.window = window
+        w = window.double().numpy()
+        if normalized:      # torchaudio functional.py:139-140: spec_f /= window.pow(2).sum().sqrt()
+            w = w / math.sqrt(float(window.pow(2.0).sum()))
+        with torch.cuda.device(self.device):
+            self._con = _Contraction(windowed_dft_taps(w, N), H, (W - H) // 2, self.device)
+            nz = self.fb != 0
+            any_nz = nz.any(dim=0)
+            k_idx = torch.arange(self.fb.shape[0])
+            lo = torch.where(nz, k_idx[:, None], self.fb.shape[0]).min(dim=0).values
+            hi = torch.where(nz, k_idx[:, None], -1).max(dim=0).values
+            lo = torch.where(any_nz, lo, torch.ones_like(lo))
+            hi = torch.where(any_nz, hi, torch.zeros_like(hi))
+            self._krange = torch.stack([lo, hi], dim=1).to(torch.int32).contiguous().to(self.device)
+            self._fbT = self.fb.t().contiguous().to(self.device)
+        self._norms: Optional[torch.Tensor] = None
+        self.first_bin, self.num_bins, self.live_bins = 0, N // 2 + 1, N // 2 + 1
+        self.last_launches = 0
+
+    def set_norms(self, norms: Optional[torch.Tensor]) -> None:
+        if norms is None:
+            self._norms = None
+            return
+        if norms.numel() != self.n_mels:
+            raise ValueError(f"mel_norms has {norms.numel()} entries, expected {self.n_mels}")
+        self._norms = norms.detach().to(device=self.device, dtype=torch.float32).contiguous().clone()
+
+    def frames(self, length: int) -> int:
+        if length <= self.pad or length + 2 * self.pad < self.n_fft:
+            raise RuntimeError(
+                f"Argument #4: Padding size should be less than the corresponding input dimension, but got: "
+                f"padding ({self.pad}, {self.pad}) at dimension 1 of input of length {length}")
+        return 1 + (length + 2 * self.pad - self.n_fft) // self.hop
+
+    def forward(self, wav: torch.Tensor, lengths: Optional[torch.Tensor] = None, *, want_mask: bool = False,
+                impl: str = "tcgen05", debug_reim: bool = False, t_max: Optional[int] = None,
+                stats_acc: Optional[torch.Tensor] = None):
+        from .stft import framed_contraction
+        if impl != "tcgen05" or debug_reim or stats_acc is not None:
+            raise NotImplementedError("the general-shape path has the tcgen05 contraction only (no cross-check kernel, "
+                                      "no DFT-stage dump, no fused statistics)")
+        if wav.device != self.device:
+            raise RuntimeError(f"input on {wav.device}, plan on {self.device}")
+        if wav.dtype != torch.float32 or wav.dim() != 2:
+            raise RuntimeError("GeneralMelPlan.forward expects a 2-D float32 tensor")
+        if wav.stride(1) != 1 or (wav.shape[0] > 1 and wav.stride(0) < wav.shape[1]):
+            wav = wav.contiguous()
+        B, Lmax = int(wav.shape[0]), int(wav.shape[1])
+        if B == 0:
+            raise RuntimeError("empty batch")
+        T_full = self.frames(Lmax)
+        T = T_full if t_max is None else int(t_max)
+        lib = self._lib
+        N, H, W = self.n_fft, self.hop, self.win_length
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            len_dev = None
+            if lengths is not None:
+                len_dev = lengths.to(device=self.device, dtype=torch.int64).contiguous()
+                if len_dev.numel() != B:
+                    raise ValueError("lengths must have one entry per clip")
+                nf64 = 1 + torch.div(len_dev + (2 * self.pad - N), H, rounding_mode="floor")
+                ok = (len_dev > self.pad) & (len_dev + 2 * self.pad >= N) & (len_dev <= Lmax)
+                n_frames = torch.where(ok, nf64, torch.zeros_like(nf64)).clamp_(max=T).to(torch.int32)
+            else:
+                n_frames = torch.full((B,), min(T_full, T), dtype=torch.int32, device=self.device)
+            y, d, Trows = framed_contraction(lib, self._con, wav, len_dev, N, H, W, self.pad, self.device)
+            out = torch.empty((B, T, self.n_mels), dtype=torch.float32, device=self.device)
+            nb = N // 2 + 1
+            _cabi.check(lib.ttts_stft_logmel(y.data_ptr(), int(y.stride(0)), d, 2 * nb, B, min(Trows, T),
+                                             n_frames.data_ptr(), T, nb, self._fbT.data_ptr(), self._krange.data_ptr(),
+                                             self.n_mels, self.power, self.power_eps, self.clamp,
+                                             self._norms.data_ptr() if self._norms is not None else None,
+                                             out.data_ptr(), stream))
+            mask = None
+            if want_mask:
+                mask = (torch.arange(T, device=self.device)[None, :] >= n_frames[:, None]).to(torch.uint8)
+            self.last_launches = 4
+        return out, n_frames, mask
+
+    def status(self) -> None:
+        """Nothing device-side to report: every length is checked where the frame counts are computed."""
+        torch.cuda.synchronize(self.device)
+
+
+def make_plan(**kwargs):
+    """``MelPlan`` (one fused kernel) for the transform size it is built for, ``GeneralMelPlan`` for every other one."""
+    if int(kwargs["n_fft"]) == 1024 and int(kwargs["hop_length"]) == 256:
+        return MelPlan(**kwargs)
+    return GeneralMelPlan(**kwargs)
+
+
 class _MelModuleBase(nn.Module):
     """Shared forward logic of the two reference modules."""
 
@@ -214,12 +341,12 @@ class _MelModuleBase(nn.Module):
     def _norms(self) -> Optional[torch.Tensor]:
         return None
 
-    def _plan_for(self, device: torch.device) -> MelPlan:
+    def _plan_for(self, device: torch.device):
         plans = self.__dict__.setdefault("_plans", {})
         key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
         plan = plans.get(key)
         if plan is None:
-            plan = MelPlan(device=torch.device(*key), **self._plan_kwargs())
+            plan = make_plan(device=torch.device(*key), **self._plan_kwargs())
             plans[key] = plan
             plan._norms_key = None
         norms = self._norms()

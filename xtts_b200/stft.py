@@ -64,6 +64,52 @@ class _Contraction:
         return out
 
 
+def windowed_dft_taps(window: np.ndarray, n_fft: int) -> np.ndarray:
+    """[2 * bins, win] float64: row 2k = w[n] cos(2 pi k m / N), row 2k + 1 = -w[n] sin(.), m = n + (N - win) / 2 (the
+    window sits centred in the n_fft frame, as torch.stft pads it)."""
+    N, W = int(n_fft), int(window.shape[0])
+    nb = N // 2 + 1
+    n = np.arange(W, dtype=np.int64) + (N - W) // 2
+    k = np.arange(nb, dtype=np.int64)
+    ang = 2.0 * np.pi * ((k[:, None] * n[None, :]) % N) / N
+    taps = np.empty((2 * nb, W), dtype=np.float64)
+    taps[0::2] = np.cos(ang) * window[None, :]
+    taps[1::2] = -np.sin(ang) * window[None, :]
+    return taps
+
+
+def framed_contraction(lib, con: "_Contraction", x: torch.Tensor, lengths_dev: Optional[torch.Tensor], N: int, H: int,
+                       W: int, pad: int, device: torch.device):
+    """Reflect-pad every clip by ``pad`` at its OWN length (torch.stft(center=True): pad = N / 2) and run the windowed-DFT
+    contraction over it.  Returns (y [B, rows * 2 * bins], d, T): frame t of clip b is row d + t of y[b], T = the frame
+    count of the full width.  The contraction's zero-padding convention puts d = ceil(width / H) rows before frame 0, so
+    the padded clip is offset (and given a zero margin when the window fills the frame) to make row d + t frame t."""
+    B, L = int(x.shape[0]), int(x.shape[1])
+    if L <= pad or L + 2 * pad < N:
+        raise RuntimeError(f"Argument #4: Padding size should be less than the corresponding input dimension, but got: "
+                           f"padding ({pad}, {pad}) at dimension 2 of input of length {L}")
+    if pad % 4:
+        raise NotImplementedError("the reflect padding must be a multiple of 4 samples here")
+    T = 1 + (L + 2 * pad - N) // H
+    width = con.width
+    d = -(-width // H)                                  # leading rows of the contraction that precede frame 0
+    off0 = (N - W) // 2 - (d * H - width)               # where row 0 of the contraction starts in the padded clip
+    margin = (max(0, -off0) + 3) // 4 * 4               # rows before frame 0 may start left of it: zeros there
+    length = (T + d) * H + width                        # samples the contraction may read per clip
+    rows = -(-length // H)
+    Lp = (max(off0, 0) + rows * H + W + 8 + margin + 3) // 4 * 4
+    Lp = max(Lp, (L + 2 * pad + margin + 3) // 4 * 4)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    flat = torch.empty(B * Lp + margin, dtype=torch.float32, device=device)
+    if margin:
+        flat[:margin].zero_()
+    _cabi.check(lib.ttts_reflect_pad(x.data_ptr(), int(x.stride(0)) if B > 1 else L,
+                                     lengths_dev.data_ptr() if lengths_dev is not None else None, B, L, pad,
+                                     flat.data_ptr() + 4 * margin, Lp, stream))
+    xv = flat.as_strided((B, Lp - max(off0, 0)), (Lp, 1), margin + off0)
+    return con(xv, length), d, T
+
+
 def _device_of(x: torch.Tensor) -> torch.device:
     if not x.is_cuda:
         raise RuntimeError("xtts_b200.stft runs on CUDA sm_100a only; there is no CPU fallback")
@@ -98,16 +144,10 @@ class TorchSTFT(nn.Module):
         key = (device.index, self.window._version)
         if key not in plans:
             N, W = self.n_fft, self.win_length
-            nb = N // 2 + 1
             w = self.window.detach().double().cpu().numpy()
             if self.normalized:
                 w = w / math.sqrt(N)                          # torch.stft(normalized=True): frame_length ** -0.5
-            n = np.arange(W, dtype=np.int64) + (N - W) // 2    # the window sits centred in the n_fft frame
-            k = np.arange(nb, dtype=np.int64)
-            ang = 2.0 * np.pi * ((k[:, None] * n[None, :]) % N) / N
-            taps = np.empty((2 * nb, W), dtype=np.float64)
-            taps[0::2] = np.cos(ang) * w[None, :]
-            taps[1::2] = -np.sin(ang) * w[None, :]
+            taps = windowed_dft_taps(w, N)
             plans[key] = _Contraction(taps, self.hop_length, (W - self.hop_length) // 2, device)
         return plans[key]
 
@@ -141,27 +181,8 @@ class TorchSTFT(nn.Module):
                                                  x0.data_ptr(), Lp0, stream))
                 x = x0[:, :L0 + 2 * p0]
             B, L = int(x.shape[0]), int(x.shape[1])
-            pad = N // 2
-            if L <= pad:
-                raise RuntimeError(f"Argument #4: Padding size should be less than the corresponding input dimension, but got: "
-                                   f"padding ({pad}, {pad}) at dimension 2 of input of length {L}")
-            T = 1 + L // H
             con = self._plan(device)
-            width = con.width
-            d = -(-width // H)                                  # leading rows of the contraction that precede frame 0
-            off0 = (N - W) // 2 - (d * H - width)               # where row 0 of the contraction starts in the padded clip
-            margin = (max(0, -off0) + 3) // 4 * 4               # rows before frame 0 may start left of it: zeros there
-            length = (T + d) * H + width                        # samples the contraction may read per clip
-            rows = -(-length // H)
-            Lp = (max(off0, 0) + rows * H + W + 8 + margin + 3) // 4 * 4
-            Lp = max(Lp, (L + 2 * pad + margin + 3) // 4 * 4)
-            flat = torch.empty(B * Lp + margin, dtype=torch.float32, device=device)
-            if margin:
-                flat[:margin].zero_()
-            _cabi.check(lib.ttts_reflect_pad(x.data_ptr(), int(x.stride(0)) if B > 1 else L, None, B, L, pad,
-                                             flat.data_ptr() + 4 * margin, Lp, stream))
-            xv = flat.as_strided((B, Lp - max(off0, 0)), (Lp, 1), margin + off0)
-            y = con(xv, length)                                 # [B, rows * 2 * bins]: row d + t = frame t, (re, im) pairs
+            y, d, T = framed_contraction(lib, con, x, None, N, H, W, N // 2, device)   # row d + t = frame t, (re, im) pairs
             nb = N // 2 + 1
             out = torch.empty((B, nb, T), dtype=torch.float32, device=device)
             power = float(self.power) if self.power is not None else 0.0
