@@ -244,19 +244,26 @@ class GeneralMelPlan:
         w = window.double().numpy()
         if normalized:      # torchaudio functional.py:139-140: spec_f /= window.pow(2).sum().sqrt()
             w = w / math.sqrt(float(window.pow(2.0).sum()))
+        # bin pruning (as the fused kernel): only the DFT rows some filter weighs are computed
+        live = torch.nonzero((self.fb != 0).any(dim=1)).flatten()
+        if live.numel() == 0:
+            raise ValueError("filterbank is all zero")
+        self.first_bin, kmax = int(live[0]), int(live[-1])
+        self.live_bins = self.num_bins = kmax - self.first_bin + 1
+        fbl = self.fb[self.first_bin:kmax + 1]               # [live bins, n_mels]
         with torch.cuda.device(self.device):
-            self._con = _Contraction(windowed_dft_taps(w, N), H, (W - H) // 2, self.device)
-            nz = self.fb != 0
+            taps = windowed_dft_taps(w, N)[2 * self.first_bin:2 * (kmax + 1)]
+            self._con = _Contraction(taps, H, (W - H) // 2, self.device)
+            nz = fbl != 0
             any_nz = nz.any(dim=0)
-            k_idx = torch.arange(self.fb.shape[0])
-            lo = torch.where(nz, k_idx[:, None], self.fb.shape[0]).min(dim=0).values
+            k_idx = torch.arange(fbl.shape[0])
+            lo = torch.where(nz, k_idx[:, None], fbl.shape[0]).min(dim=0).values
             hi = torch.where(nz, k_idx[:, None], -1).max(dim=0).values
             lo = torch.where(any_nz, lo, torch.ones_like(lo))
             hi = torch.where(any_nz, hi, torch.zeros_like(hi))
             self._krange = torch.stack([lo, hi], dim=1).to(torch.int32).contiguous().to(self.device)
-            self._fbT = self.fb.t().contiguous().to(self.device)
+            self._fbT = fbl.t().contiguous().to(self.device)
         self._norms: Optional[torch.Tensor] = None
-        self.first_bin, self.num_bins, self.live_bins = 0, N // 2 + 1, N // 2 + 1
         self.last_launches = 0
 
     def set_norms(self, norms: Optional[torch.Tensor]) -> None:
@@ -308,7 +315,7 @@ class GeneralMelPlan:
                 n_frames = torch.full((B,), min(T_full, T), dtype=torch.int32, device=self.device)
             y, d, Trows = framed_contraction(lib, self._con, wav, len_dev, N, H, W, self.pad, self.device)
             out = torch.empty((B, T, self.n_mels), dtype=torch.float32, device=self.device)
-            nb = N // 2 + 1
+            nb = self.live_bins
             _cabi.check(lib.ttts_stft_logmel(y.data_ptr(), int(y.stride(0)), d, 2 * nb, B, min(Trows, T),
                                              n_frames.data_ptr(), T, nb, self._fbT.data_ptr(), self._krange.data_ptr(),
                                              self.n_mels, self.power, self.power_eps, self.clamp,
