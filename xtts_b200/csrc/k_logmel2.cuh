@@ -347,6 +347,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
   // Programmatic dependent launch: everything above (plan constants, barriers, TMEM) overlaps k_prep, which produces
   // the frame counts, group prefix and edge buffers read below.
   asm volatile("griddepcontrol.wait;" ::: "memory");
+#if TTTS_PREP_PDL
+  asm volatile("griddepcontrol.launch_dependents;");   // the next call's k_prep may be staged now (it waits for this grid's end)
+#endif
   tc_fence_before();
   if (kPair) cluster_sync_all(); else __syncthreads();       // pair: the peer's barriers must exist before anyone arrives on them
   tc_fence_after();

@@ -46,6 +46,9 @@
 // ------------------------------------------------------------------------------------------
 namespace {
 
+#ifndef TTTS_PREP_PDL
+#define TTTS_PREP_PDL 1      /* k_prep as a programmatic dependent of the previous kernel in the stream: -1 % per step (profiles/r3a) */
+#endif
 constexpr int kNfft = 1024;            // the only transform size built this round
 constexpr int kHop = 256;
 constexpr int kKfold = kNfft / 2;      // folded contraction length (kappa = n-1, n = 1..512)
@@ -678,6 +681,11 @@ __global__ void __launch_bounds__(1024) k_prep(const float* __restrict__ wav, in
                                                int32_t* __restrict__ n_frames_user, int64_t* __restrict__ frame_off,
                                                int64_t* __restrict__ group_off, int32_t* __restrict__ status,
                                                unsigned long long* __restrict__ stat_ws) {
+#if TTTS_PREP_PDL
+  // k_prep is itself a programmatic dependent of whatever precedes it in the stream (the previous call's k_logmel2, which
+  // triggers early): its launch is staged while that kernel still runs; nothing is read or written before the wait
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
   asm volatile("griddepcontrol.launch_dependents;");   // the fused kernel may start its prologue (it waits for this grid's end)
   if (blockIdx.x > 0) {
     clip_body(wav, row_stride, lengths, Lmax, pad, Tmax, edge, out, n_mels, mask, (blockIdx.x - 1) / kPrepSplit,
@@ -1378,9 +1386,23 @@ int forward_impl(const ttts_mel_plan* p, const float* wav, int64_t row_stride, c
   // the reflect padding go through a small edge buffer.  Otherwise (and for k_simt) the clips are padded
   // into the workspace first.
   const bool direct = in_place;
+#if TTTS_PREP_PDL
+  {
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3((unsigned)(kPrepSplit * B + 1)); lc.blockDim = dim3(1024); lc.dynamicSmemBytes = 0; lc.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&lc, k_prep, wav, row_stride, direct ? w.edge : (float*)nullptr, out, (int)p->cfg.n_mels, mask, lengths,
+                                (int)B, Lmax, (int)p->cfg.pad, (int)Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off,
+                                w.status, stat_acc ? w.stat : (unsigned long long*)nullptr));
+  }
+#else
   k_prep<<<kPrepSplit * B + 1, 1024, 0, stream>>>(wav, row_stride, direct ? w.edge : nullptr, out, p->cfg.n_mels, mask, lengths, B, Lmax,
                                      p->cfg.pad, Tmax, w.n_frames, n_frames_user, w.frame_off, w.group_off, w.status,
                                      stat_acc ? w.stat : nullptr);
+#endif
   ++g_launches;
   if (!direct) {
     const int64_t vecs = (w.Lp + 3) / 4;
