@@ -10,7 +10,7 @@ dev = torch.device("cuda:0")
 plan = MelPlan(sample_rate=22050, n_fft=1024, hop_length=256, win_length=1024, n_mels=80, f_min=0, f_max=8000,
                power=2.0, norm="slaney", device=dev, lab=True)
 for seed in range(8):
-    g = torch.Generator(device=dev, lab=True).manual_seed(seed)
+    g = torch.Generator(device=dev).manual_seed(seed)
     x = torch.rand(64, 220500, device=dev, generator=g) * 2 - 1
     outs = []
     for rep in range(4):
