@@ -640,3 +640,21 @@ def test_general_transform_sizes_ragged_batch_and_batch_size(dev):
         assert float(np.abs(_np(yb[b:b + 1]) - ref).max()) <= TOL, b
     with pytest.raises(RuntimeError):
         m(torch.zeros(1, 1024, device=dev))                          # reflect pad 1024 needs more than 1024 samples
+
+
+def test_nan_samples_poison_exactly_the_frames_the_reference_poisons(dev, v1):
+    """torch.clamp keeps NaN, so one NaN sample makes every mel of the frames that contain it NaN in the reference (the FFT
+    spreads it over all bins); everything else must stay within the usual tolerance.  (A NaN that sits exactly on a frame's
+    first tap is dropped here with the zero window value the reference multiplies it by: positions off the hop grid.)"""
+    from xtts_b200 import MelSpectrogramFeatures
+    x = orc.synth("uniform", 3, 30000, 31)
+    x[0, 7003] = np.nan
+    x[2, 29990] = np.nan                                  # inside the last frames and the reflected tail
+    for mod, cfg, norms in ((v1, orc.V1, orc.default_mel_norms(80)), (MelSpectrogramFeatures(), orc.V2, None)):
+        y = _np(mod(torch.from_numpy(x).to(dev)))
+        ref = orc.callsite_logmel(x, cfg, norms).numpy()
+        assert np.array_equal(np.isnan(y), np.isnan(ref))
+        assert np.isnan(ref[0]).any() and np.isnan(ref[2]).any() and not np.isnan(ref[1]).any()
+        ok = ~np.isnan(ref)
+        bar = TOL if cfg is orc.V1 else np.maximum(TOL, 2e-5 / np.exp(np.where(ok, ref, 0.0)))
+        assert (np.abs(y - ref)[ok] <= (bar if np.isscalar(bar) else bar[ok])).all()

@@ -868,9 +868,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 #if F2_FAST_LOG
                   // lg2.approx * ln 2 (<= 3 ulp of the result away from 1, 2^-21.4 absolute near it) instead of logf's ~20
                   // instructions; values at or below the clamp take the exactly rounded constant, so silence stays bit-exact
-                  const float x = v[i][k] > P.clamp ? __logf(v[i][k]) : log_clamp;
+                  const float x = !(v[i][k] <= P.clamp) ? __logf(v[i][k]) : log_clamp;   // (NaN goes through the log, as torch.clamp keeps it)
 #else
-                  const float x = logf(fmaxf(v[i][k], P.clamp));
+                  const float x = logf(v[i][k] < P.clamp ? P.clamp : v[i][k]);
 #endif
                   if (P.stat_ws && rowp[i]) {
                     // stage (4), fused: per-channel sum / sum of squares of the UN-normalised log-mel in 64-bit fixed point

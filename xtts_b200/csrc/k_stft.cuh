@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256) k_stft_logmel(const float* __restrict__ y
       const float* pw = s_pw + r * pitch;
       float acc = 0.f;
       for (int k = kr.x; k <= kr.y; ++k) acc = fmaf(__ldg(w + k), pw[k], acc);
-      v = logf(fmaxf(acc, clamp));
+      v = logf(acc < clamp ? clamp : acc);               // torch.clamp keeps NaN (fmaxf would not)
       if (norms) v = v / norms[m];
     }
     out[((long long)b * Tmax + t) * n_mels + m] = v;

@@ -1202,7 +1202,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_logmel(const LogmelParams P) {
         float* rowp = reinterpret_cast<float*>((uintptr_t)pr);
         const float* parked = s_park + (q * 32 + rr) * park_pitch;
         for (int mth = lane; mth < P.n_mels; mth += 32)
-          rowp[mth] = logf(fmaxf(parked[mth], P.clamp)) / s_norm[mth];   // true division, as the reference
+          rowp[mth] = logf(parked[mth] < P.clamp ? P.clamp : parked[mth]) / s_norm[mth];   // true division, as the reference
       }
       __syncwarp();
     }
@@ -1281,7 +1281,7 @@ __global__ void __launch_bounds__(kSimtThreads) k_simt(const float* __restrict__
     if (s_out[f] < 0) continue;
     float acc = 0.f;
     for (int i = 0; i < nbt; ++i) acc = fmaf(sP[f * nbt + i], fb[(size_t)i * n_mels + m], acc);
-    float y = logf(fmaxf(acc, clamp));
+    float y = logf(acc < clamp ? clamp : acc);
     if (norms) y = y / norms[m];
     out[s_out[f] + m] = y;
   }
