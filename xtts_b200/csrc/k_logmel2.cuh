@@ -42,7 +42,16 @@ constexpr int kSets = F2_SETS;                   // converter sets: set s serves
 constexpr int kAStages2 = F2_ASTAGES;            // A-operand TMEM stages (k-step sequence number mod 4): 128 columns
 constexpr int kAccStride2 = F2_ACC_STRIDE;        // columns between the Re and Im accumulators; the A ring starts at twice that
                                                  // (8 stages in V2's spare columns: no gain, and the run-time depth cost V1 3 %: profiles/r2g_variants.txt)
-constexpr int kKS = 33;                          // k-steps per pass: 32 x 8 folded taps + the centre tap
+#ifndef F2_CENTRE_EPI
+#define F2_CENTRE_EPI 1
+#endif
+// The centre tap E'[512] = w[512] f[512] (basis +-1: a rank-1 term) can be added by the epilogue instead of costing a 33rd
+// k-step (handshake, conversion, 3 MMAs): -5.7 % on the magnitude plans (V2), -3.2 % on V1 (profiles/r3b).  1: magnitude plans
+// only -- on V1 the changed rounding order moves ONE element of the committed tone golden from 0.96 to 1.006 of its
+// dual-oracle bound (a mel value of 2e-5 next to the clamp floor, cancellation regime: tools/gpu_tone_stage_diag.py), so V1
+// keeps the 33rd k-step; 2: every plan; 0: none.
+constexpr int kCentreEpiMode = F2_CENTRE_EPI;
+constexpr int kKStab = 33;                       // basis stages per pass in the plan's table: 32 x 8 folded taps + the centre tap
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
 constexpr int kSlotFloats = 20;                  // 12 forward taps + 8 mirrored taps; 80 B pitch: conflict-free LDS.128
 constexpr int kStageBytes = kSlots * kSlotFloats * 4;
@@ -294,6 +303,8 @@ __device__ __forceinline__ void tc_commit2(uint32_t bar) {
 template <bool kPower1, bool kDebug, bool kPair>
 __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P) {
   using namespace f2;
+  constexpr bool kCentreEpi = kCentreEpiMode == 2 || (kCentreEpiMode == 1 && kPower1);
+  constexpr int kKS = kCentreEpi ? 32 : 33;                // k-steps per pass the pipeline runs
   constexpr int kBS = kPair ? kBStagesPair : kBStages2;    // basis ring depth
   constexpr int kRegsConvT = kPower1 ? F2_REGS_CONV_P1 : kRegsConv, kRegsEpiT = kPower1 ? F2_REGS_EPI_P1 : kRegsEpi;
   constexpr int kHold = kPower1 ? F2_HOLD_P1 : F2_HOLD;    // trailing bins of an epilogue chain held in registers
@@ -374,7 +385,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
             const uint32_t full = smem_u32(&bars->b_full[st]);
             mbar_expect_tx(full, b_stage_bytes);
             bulk_g2s(smem_u32(s_b + (size_t)st * b_stage_bytes),
-                     P.basis + (((size_t)ps * kKS + ks) * (kPair ? 2 : 1) + cta_rank) * (b_stage_bytes / 4), b_stage_bytes, full);
+                     P.basis + (((size_t)ps * kKStab + ks) * (kPair ? 2 : 1) + cta_rank) * (b_stage_bytes / 4), b_stage_bytes, full);
           }
     }
     __syncwarp();
@@ -437,7 +448,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
               mma(d_re, e_lo, c_hi, first);                  // small terms first
               mma(d_re, e_hi, c_lo, 1u);
               mma(d_re, e_hi, c_hi, 1u);
-              if (ks < kKS - 1) {                            // the centre-tap k-step has no sine part
+              if (kCentreEpi || ks < kKS - 1) {              // the centre-tap k-step has no sine part
                 mma(d_im, o_lo, s_hi, first);
                 mma(d_im, o_hi, s_lo, 1u);
                 mma(d_im, o_hi, s_hi, 1u);
@@ -513,7 +524,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       for (int i = 0; i < kPieceIters; ++i) live |= (pc_dst[i] >> 31) << i;
       plain = __all_sync(0xffffffffu, okm == live && edm == 0);
       const int t = gi.t0 + lane;
-      if (t < gi.T) {
+      if (!kCentreEpi && t < gi.T) {
         bool edge;
         const int32_t o = sample_offset(P, gi.b, gi.T, t, kNfft / 2, &edge);
         xc_next = __ldg((edge ? edge_p : src_p) + o);
@@ -522,7 +533,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
 
     Cursor ic{(int)blockIdx.x, 0, set};                // issue cursor, kDepth own k-steps ahead of the consume cursor
     auto issue = [&](uint32_t stage) {
-      if (ic.tile < num_tiles && ic.ks < kKS - 1 && !(P.exp_flags & 128)) {   // 128: timing experiment, no raw-audio loads
+      if (ic.tile < num_tiles && (kCentreEpi || ic.ks < kKS - 1) && !(P.exp_flags & 128)) {   // 128: timing experiment, no raw-audio loads
         const uint32_t base = smem_u32(my_raw + (size_t)stage * kStageBytes);
         const int adv = kKStep * ic.ks;
         if (plain) {                                   // warp-uniform: interior groups (all but the first / last of a clip)
@@ -561,7 +572,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
       __syncwarp();
       uint32_t ehi[8], elo[8], ohi[8], olo[8];
-      const bool centre = cc.ks == kKS - 1;
+      const bool centre = !kCentreEpi && cc.ks == kKS - 1;
       if (!centre) {
         const float4* s0 = reinterpret_cast<const float4*>(my_raw + (size_t)stage * kStageBytes) + lane * 5;
         const float4* s2 = s0 + 10;                    // slot lane + 2
@@ -644,7 +655,18 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       // out of line).  A closed filter's partial sum is added to its parked sum (`old`, prefetched one close ahead; the
       // park rows start a tile zeroed).  The filters still open at the end of a chain are shared with the next chain, so
       // they go through s_fl and chain 0's warp adds them once all four chains of the quarter are done.
+      float ec = 0.f;                                    // w[512] f[512] of my row: the centre tap, added to Re with the parity's sign
+      if (kCentreEpi) {
+        const GroupInfo gc = locate_group(P, (int64_t)tile * 4 + q, total_groups);
+        const int tc = gc.t0 + lane;
+        if (gc.valid && tc < gc.T) {
+          bool edge;
+          const int32_t o = sample_offset(P, gc.b, gc.T, tc, kNfft / 2, &edge);
+          ec = P.wc * __ldg((edge ? P.edge : P.src) + o);
+        }
+      }
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
+        const float ecs = (ps >= P.sp) ? -ec : ec;       // passes [0, sp): even bins, cos(pi k) = +1; [sp, 2 sp): odd bins, -1
         ScanState sc;
         sc.run_lo = 0.f; sc.run_hi = 0.f;
         sc.pa = pa0 + 4u * (uint32_t)P.cstart[ps * kChains + ch];
@@ -727,7 +749,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           }
         };
         auto power_of = [&](uint32_t re, uint32_t im) {
-          const float a = __uint_as_float(re), bq = __uint_as_float(im);
+          const float a = kCentreEpi ? __uint_as_float(re) + ecs : __uint_as_float(re), bq = __uint_as_float(im);
           float pw = fmaf(a, a, bq * bq);
           if (kPower1) {
 #if F2_SQRT_APPROX
@@ -771,7 +793,7 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
                   const int k = P.first_k[par] + 2 * (sub * nb + ch * cb + r16 + 4 * qr + j);
                   if (k <= P.kmax) {
                     float* d = P.dbg_reim + gdbg * (2 * P.dbg_nbt) + (k - P.dbg_kmin);
-                    d[0] = __uint_as_float(re[j]);
+                    d[0] = kCentreEpi ? __uint_as_float(re[j]) + ecs : __uint_as_float(re[j]);
                     d[P.dbg_nbt] = __uint_as_float(im[j]);
                   }
                 }
