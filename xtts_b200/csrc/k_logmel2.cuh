@@ -43,13 +43,15 @@ constexpr int kAStages2 = F2_ASTAGES;            // A-operand TMEM stages (k-ste
 constexpr int kAccStride2 = F2_ACC_STRIDE;        // columns between the Re and Im accumulators; the A ring starts at twice that
                                                  // (8 stages in V2's spare columns: no gain, and the run-time depth cost V1 3 %: profiles/r2g_variants.txt)
 #ifndef F2_CENTRE_EPI
-#define F2_CENTRE_EPI 1
+#define F2_CENTRE_EPI 2
 #endif
-// The centre tap E'[512] = w[512] f[512] (basis +-1: a rank-1 term) can be added by the epilogue instead of costing a 33rd
-// k-step (handshake, conversion, 3 MMAs): -5.7 % on the magnitude plans (V2), -3.2 % on V1 (profiles/r3b).  1: magnitude plans
-// only -- on V1 the changed rounding order moves ONE element of the committed tone golden from 0.96 to 1.006 of its
-// dual-oracle bound (a mel value of 2e-5 next to the clamp floor, cancellation regime: tools/gpu_tone_stage_diag.py), so V1
-// keeps the 33rd k-step; 2: every plan; 0: none.
+// The centre tap E'[512] = w[512] f[512] (basis +-1: a rank-1 term) is added by the epilogue instead of costing a 33rd
+// k-step (handshake, conversion, 3 MMAs): -5.7 % on the magnitude plans (V2), -1.7 % on V1 (profiles/r3b, r3c).  Magnitude
+// plans add it with one FADD.  Power plans (V1) repeat the two accumulations the 33rd k-step performed -- D += tf32(e_lo) * (+-1),
+// then D += e_hi * (+-1), the operand truncated as the tensor core truncates it: a plain FADD changed the rounding enough to
+// move ONE element of the committed tone golden from 0.959 to 1.006 of its dual-oracle bound (a mel value of 2e-5 next to
+// the clamp floor, cancellation regime: tools/gpu_tone_stage_diag.py); with the two-step form that element is
+// bit-identical to the 33-k-step kernel's.  2: every plan; 1: magnitude plans only; 0: none (33 k-steps).
 constexpr int kCentreEpiMode = F2_CENTRE_EPI;
 constexpr int kKStab = 33;                       // basis stages per pass in the plan's table: 32 x 8 folded taps + the centre tap
 constexpr int kSlots = 34;                       // staged slots per warp and k-step (32 rows + 2)
@@ -667,6 +669,9 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
       }
       for (int ps = 0; ps < P.passes; ++ps, ++pseq) {
         const float ecs = (ps >= P.sp) ? -ec : ec;       // passes [0, sp): even bins, cos(pi k) = +1; [sp, 2 sp): odd bins, -1
+        // power plans: the 33rd k-step's two accumulations, D += tf32(e_lo) * (+-1), D += e_hi * (+-1)
+        const float ecs_hi = __uint_as_float(__float_as_uint(ecs) & 0xFFFFE000u);
+        const float ecs_lo = __uint_as_float(__float_as_uint(ecs - ecs_hi) & 0xFFFFE000u);
         ScanState sc;
         sc.run_lo = 0.f; sc.run_hi = 0.f;
         sc.pa = pa0 + 4u * (uint32_t)P.cstart[ps * kChains + ch];
@@ -749,7 +754,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
           }
         };
         auto power_of = [&](uint32_t re, uint32_t im) {
-          const float a = kCentreEpi ? __uint_as_float(re) + ecs : __uint_as_float(re), bq = __uint_as_float(im);
+          const float r0 = __uint_as_float(re), bq = __uint_as_float(im);
+          const float a = !kCentreEpi ? r0 : kPower1 ? r0 + ecs : __fadd_rn(__fadd_rn(r0, ecs_lo), ecs_hi);
           float pw = fmaf(a, a, bq * bq);
           if (kPower1) {
 #if F2_SQRT_APPROX
@@ -793,7 +799,8 @@ __global__ void __launch_bounds__(f2::kThreads2, 1) k_logmel2(const f2::Params P
                   const int k = P.first_k[par] + 2 * (sub * nb + ch * cb + r16 + 4 * qr + j);
                   if (k <= P.kmax) {
                     float* d = P.dbg_reim + gdbg * (2 * P.dbg_nbt) + (k - P.dbg_kmin);
-                    d[0] = kCentreEpi ? __uint_as_float(re[j]) + ecs : __uint_as_float(re[j]);
+                    d[0] = !kCentreEpi ? __uint_as_float(re[j]) : kPower1 ? __uint_as_float(re[j]) + ecs
+                                                                            : __fadd_rn(__fadd_rn(__uint_as_float(re[j]), ecs_lo), ecs_hi);
                     d[P.dbg_nbt] = __uint_as_float(im[j]);
                   }
                 }
