@@ -42,8 +42,8 @@ FLOP_PER_FRAME_V2 = 2.0 * 1024 * 1026 + 3 * 513 + 2 * 513 * 100 + 513 + 200   # 
 BYTES_PER_FRAME = 1344.0          # 1024 B in + 320 B out
 # tensor FLOP k_logmel2 actually issues per frame: 2 parities x sp sub-passes x [33 cos + 32 sin k-steps] x 3 TF32
 # products x 2 * nb * 8  (V1: sp 1, nb 192; V2: sp 2, nb 128)
-EXEC_FLOP_PER_FRAME = 2 * (33 + 32) * 3 * 2 * 192 * 8
-EXEC_FLOP_PER_FRAME_V2 = 2 * 2 * (33 + 32) * 3 * 2 * 128 * 8
+EXEC_FLOP_PER_FRAME = 2 * (32 + 32) * 3 * 2 * 192 * 8      # the centre tap is added by the epilogue: 32 cosine k-steps
+EXEC_FLOP_PER_FRAME_V2 = 2 * 2 * (32 + 32) * 3 * 2 * 128 * 8
 WORKLOAD = "64x10s_22050Hz_uniform[-1,1)_TorchMelSpectrogram_V1"
 ROTATE = 4                        # distinct input batches: 4 x 56.4 MB = 226 MB > 126 MB L2
 MIN_REGION_S = 0.5
