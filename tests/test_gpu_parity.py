@@ -340,6 +340,13 @@ def test_v3_librosa_style_mel_spectrogram(dev):
         assert np.abs(_np(y) - ref).max() <= TOL, L
     y2 = mel_spectrogram(torch.from_numpy(x).to(dev), 1024, 80, 24000, 256, 1024, 0, 8000, center=False)
     assert torch.equal(y, y2)
+    # another transform size through the same function (the general-shape path): n_fft 2048, hop 512
+    import dataclasses
+    cfg = dataclasses.replace(orc.V3, n_fft=2048, hop=512, win_length=2048, pre_pad=(2048 - 512) // 2)
+    x = orc.synth("uniform", 2, 30000, 77)
+    y3 = mel_spectrogram(torch.from_numpy(x).to(dev), 2048, 80, 24000, 512, 2048, 0, 8000, center=False)
+    ref = orc.callsite_logmel(x, cfg).numpy()
+    assert tuple(y3.shape) == ref.shape and np.abs(_np(y3) - ref).max() <= TOL
 
 
 def test_group_layout_frame_counts_around_multiples_of_32(dev, v1):

@@ -490,7 +490,7 @@ def mel_spectrogram(y, n_fft, num_mels, sampling_rate, hop_size, win_size, fmin,
     plan = _V3_PLANS.get(key)
     if plan is None:
         fb = librosa_mel(sampling_rate, n_fft, num_mels, fmin, fmax).t().contiguous()
-        plan = _V3_PLANS[key] = MelPlan(sample_rate=sampling_rate, n_fft=n_fft, hop_length=hop_size, win_length=win_size,
+        plan = _V3_PLANS[key] = make_plan(sample_rate=sampling_rate, n_fft=n_fft, hop_length=hop_size, win_length=win_size,
                                        n_mels=num_mels, f_min=fmin, f_max=fmax, power=1.0, norm=None, clamp=1e-5,
                                        center=False, pre_pad=int((n_fft - hop_size) / 2), power_eps=1e-9, fb=fb, device=dev)
     if y.dim() == 3:
